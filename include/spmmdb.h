@@ -1,0 +1,142 @@
+/*
+ * spmmdb.h -- C ABI of the B200-native SpMM engine (libspmmdb.so).
+ *
+ * This is the drop-in boundary for the reference's one data-parallel hot path
+ * (sparse adjacency A in CSR / BSR times a dense feature matrix B, plus the
+ * csr2bsr / bsr2csr conversions).  Every entry point names the reference
+ * interface it replaces (file:line in xuyifangreeneyes/spmm-denseblock).
+ *
+ * Conventions
+ *   - plain C: pointers + sizes, no C++/torch types.  Unless a function says
+ *     "host", every pointer is a DEVICE pointer owned by the caller; the
+ *     callee allocates nothing the caller sees and frees nothing.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream, as in
+ *     the reference: gespmm_csrmm.h:385-417 `<<<..., 0, 0>>>`).  Calls are
+ *     asynchronous unless stated otherwise.
+ *   - indices are 0-based int32, values fp32 (the only instantiation the
+ *     reference uses: run_csrmm.cu:144, run_bsrmm.cu:156).
+ *   - return value: SPMMDB_OK (0) or a negative spmmdb_status.  The C++
+ *     drop-in headers (include/gespmm_csrmm.h, include/rocsparse_bsrmm.h) map
+ *     these to the reference's void / cusparseStatus_t conventions.
+ *   - there is NO CPU fallback: without a CUDA device every compute entry
+ *     point returns SPMMDB_ERR_CUDA.
+ */
+#ifndef SPMMDB_H
+#define SPMMDB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  SPMMDB_OK = 0,
+  SPMMDB_ERR_INVALID_VALUE = -1,  /* cusparse: CUSPARSE_STATUS_INVALID_VALUE            */
+  SPMMDB_ERR_NOT_SUPPORTED = -2,  /* cusparse: CUSPARSE_STATUS_MATRIX_TYPE_NOT_SUPPORTED */
+  SPMMDB_ERR_CUDA = -3,           /* a CUDA runtime call failed (see spmmdb_last_error)  */
+  SPMMDB_ERR_ALLOC = -4,          /* internal workspace allocation failed                */
+  SPMMDB_ERR_ARCH = -5            /* device is not sm_100 (tcgen05 path requested)       */
+} spmmdb_status;
+
+#define SPMMDB_ROW_MAJOR 0
+#define SPMMDB_COL_MAJOR 1
+
+#define SPMMDB_DIR_ROW 0     /* CUSPARSE_DIRECTION_ROW: row-major bs x bs blocks    */
+#define SPMMDB_DIR_COLUMN 1  /* CUSPARSE_DIRECTION_COLUMN: column-major blocks      */
+
+#define SPMMDB_MATH_FP32 0   /* CUDA-core fp32 FMA, fp32 accumulate (exact path)    */
+#define SPMMDB_MATH_TF32 1   /* tcgen05 kind::tf32, fp32 accumulate in TMEM         */
+#define SPMMDB_MATH_BF16 2   /* tcgen05 kind::f16 (bf16 inputs), fp32 accumulate    */
+
+/* Library / build information. */
+const char* spmmdb_version(void);
+const char* spmmdb_last_error(void);          /* text of the last CUDA error seen */
+int spmmdb_device_sm(void);                   /* e.g. 100 on B200; <0 = no device */
+
+/* --------------------------------------------------------------------------
+ * CSR x dense:  C = alpha * A * B + beta * C
+ * Replaces gespmm_csrmm<float> / spmmWrapper<float> (gespmm_csrmm.h:379-426:
+ * row-major B and C, alpha = 1, beta = 0) and the cuSPARSE csrmm / csrmm2 call
+ * sites (run_csrmm.cu:133-142, check_result.cu:211-216: column-major C, B
+ * column-major for op(B)=N or row-major for op(B)=T).
+ *   m        rows of A (and C)           k   columns of A = rows of B
+ *   K        dense width (B_ncols / dim) nnz rowptr[m], or -1 if unknown
+ *   b_layout / c_layout  SPMMDB_ROW_MAJOR (ld >= K) or SPMMDB_COL_MAJOR
+ *   With row-major B/C, alpha == 1, beta == 0 each output element is the fp32
+ *   FMA chain in CSR order, i.e. bit-identical to the reference kernel, for
+ *   every row of at most spmmdb_csrmm_segment(nnz) non-zeros; longer rows are
+ *   summed per fixed-size segment and the segment sums added in order
+ *   (deterministic, independent of how rows are sharded over GPUs).
+ * ------------------------------------------------------------------------ */
+int spmmdb_csrmm_f32(int m, int k, int K, int64_t nnz, const int* rowptr, const int* colind,
+                     const float* val, const float* B, int64_t ldb, int b_layout, float* C,
+                     int64_t ldc, int c_layout, float alpha, float beta, void* stream);
+
+/* Row-segment length used for a matrix with `nnz` non-zeros (see above). */
+int spmmdb_csrmm_segment(int64_t nnz);
+
+/* --------------------------------------------------------------------------
+ * BSR x dense:  C = alpha * A_bsr * op(B) + beta * C
+ * Replaces rocsparse_bsrmm_template<float> (rocsparse_bsrmm.h:102-256) and the
+ * cusparseSbsrmm call sites (run_bsrmm.cu:161, check_result.cu:223-228).
+ *   dir      SPMMDB_DIR_ROW / SPMMDB_DIR_COLUMN (block storage)
+ *   trans_b  0: B column-major, ldb >= kb*bs;  1: B row-major [k][ldb], ldb >= n
+ *   C        column-major (ldc >= mb*bs) like the reference, or row-major
+ *            [mb*bs][ldc] with c_layout = SPMMDB_ROW_MAJOR (extension)
+ *   math     SPMMDB_MATH_FP32 (CUDA cores), _TF32 or _BF16 (tcgen05 tensor
+ *            cores, block_dim in {8,16,32,64}; other shapes run the fp32 kernel)
+ * Returns the mathematical product -- the reference kernel's output-column
+ * bug (rocsparse_bsrmm_impl.h:27,326,413) is not reproduced.
+ * ------------------------------------------------------------------------ */
+int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int block_dim,
+                     float alpha, const float* bsr_val, const int* bsr_rowptr,
+                     const int* bsr_colind, const float* B, int64_t ldb, float beta, float* C,
+                     int64_t ldc, int c_layout, int math, void* stream);
+
+/* --------------------------------------------------------------------------
+ * Per-block GEMM formulation of BSR SpMM (block_cublas.cu:123-136,
+ * test_block_cublas.cu:273-284): z(col-major, ld m) += A_blk(column-major
+ * bs x bs) * Y[col*bs.., :](row-major, ld dim) for every non-zero block, as ONE
+ * grouped launch instead of nnzb cublasSgemm calls.  alpha = beta = 1.
+ * ------------------------------------------------------------------------ */
+int spmmdb_block_gemm_f32(int mb, int dim, int64_t nnzb, int block_dim, const int* bsr_rowptr,
+                          const int* bsr_colind, const float* bsr_val, const float* Y, float* Z,
+                          int math, void* stream);
+
+/* --------------------------------------------------------------------------
+ * csr2bsr, phase 1: replaces cusparseXcsr2bsrNnz (run_bsrmm.cu:121,
+ * check_result.cu:173, csr2bsr.cu:176).  Writes bsr_rowptr[mb+1] (device) and
+ * returns nnzb through a HOST pointer; synchronises `stream` to do so.
+ * Column indices must be ascending inside each row (load_data.cc:179-182).
+ * ------------------------------------------------------------------------ */
+int spmmdb_csr2bsr_nnz(int m, int n, const int* rowptr, const int* colind, int block_dim,
+                       int* bsr_rowptr, int* nnzb_host, void* stream);
+
+/* csr2bsr, phase 2: replaces cusparseScsr2bsr (run_bsrmm.cu:139).  bsr_colind
+ * ascending per block row, blocks zero filled, ragged edges zero padded. */
+int spmmdb_csr2bsr_f32(int dir, int m, int n, const int* rowptr, const int* colind,
+                       const float* val, int block_dim, const int* bsr_rowptr, int* bsr_colind,
+                       float* bsr_val, void* stream);
+
+/* bsr2csr: replaces cusparseSbsr2csr (bsr2csr.cu:186-188).  Every block
+ * expands to bs*bs explicit entries (zeros kept): nnz = nnzb*bs*bs. */
+int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr, const int* bsr_colind,
+                       const float* bsr_val, int block_dim, int* csr_rowptr, int* csr_colind,
+                       float* csr_val, void* stream);
+
+/* --------------------------------------------------------------------------
+ * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all
+ * pointers are HOST pointers (pinned memory gives full PCIe rate).  Copies A and
+ * B to the device, runs the device path, copies C back and synchronises -- the
+ * state of the reference drivers before run_csrmm.cu:94-116 / after :161.
+ * ------------------------------------------------------------------------ */
+int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr, const int* h_colind,
+                          const float* h_val, const float* h_B, float* h_C, float alpha, float beta,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPMMDB_H */

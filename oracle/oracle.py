@@ -1,0 +1,277 @@
+"""ctypes/numpy front-end of the CPU oracle (oracle/spmm_oracle.c) and of the
+reference's own CPU code built into oracle/_ref (oracle/Makefile).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs.  The product package
+(spmm_denseblock_b200) never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_i64p = np.ctypeslib.ndpointer(np.int64, flags="C_CONTIGUOUS")
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+ROW_MAJOR, COL_MAJOR = 0, 1
+
+
+def build(force=False):
+    """Compile liboracle.so (and oracle/_ref when /root/reference is present)."""
+    so = os.path.join(HERE, "liboracle.so")
+    src = os.path.join(HERE, "spmm_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", HERE, "all"])
+    elif os.path.isdir("/root/reference") and not os.path.exists(os.path.join(HERE, "_ref", "libref_host.so")):
+        subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+    return so
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.oracle_csr2bsr_nnz.restype = C.c_int64
+        _lib.oracle_calculate_nnzb.restype = C.c_int64
+        _lib.oracle_divide_matrix.restype = C.c_int64
+    return _lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _opt(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def csrmm(rowptr, colind, val, B, K, ldb=None, b_layout=ROW_MAJOR, C0=None, ldc=None,
+          c_layout=ROW_MAJOR, alpha=1.0, beta=0.0):
+    """fp64-accumulated alpha*A*B + beta*C0 -> float64 [m, K] (row-major)."""
+    rowptr, colind, val, B = _i32(rowptr), _i32(colind), _f32(val), _f32(B)
+    m = rowptr.size - 1
+    k = B.size // K if ldb is None else None
+    if ldb is None:
+        ldb = K if b_layout == ROW_MAJOR else k
+    if ldc is None:
+        ldc = K if c_layout == ROW_MAJOR else m
+    out = np.zeros((m, K), np.float64)
+    c0 = None if C0 is None else _f32(C0)
+    f = lib().oracle_csrmm_f64acc
+    f.argtypes = [C.c_int, C.c_int, _i32p, _i32p, _f32p, _f32p, C.c_int64, C.c_int, C.c_void_p,
+                  C.c_int64, C.c_int, C.c_float, C.c_float, _f64p]
+    f(m, K, rowptr, colind, val, B.ravel(), ldb, b_layout, _opt(c0), ldc, c_layout, alpha, beta, out)
+    return out
+
+
+def csrmm_f32_seq(rowptr, colind, val, B, K):
+    """The reference kernel's own fp32 sequential-FMA arithmetic (row-major)."""
+    rowptr, colind, val, B = _i32(rowptr), _i32(colind), _f32(val), _f32(B)
+    m = rowptr.size - 1
+    out = np.zeros((m, K), np.float32)
+    f = lib().oracle_csrmm_f32_seq
+    f.argtypes = [C.c_int, C.c_int, _i32p, _i32p, _f32p, _f32p, C.c_int64, _f32p, C.c_int64]
+    f(m, K, rowptr, colind, val, B.ravel(), K, out, K)
+    return out
+
+
+def spmm_cc_csr(indptr, indices, dense):
+    """spmm.cc:7-25 restated (double, int64, unit weights)."""
+    indptr = np.ascontiguousarray(indptr, np.int64)
+    indices = np.ascontiguousarray(indices, np.int64)
+    dense = np.ascontiguousarray(dense, np.float64)
+    out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
+    f = lib().oracle_spmm_cc_csr
+    f.argtypes = [C.c_int64, C.c_int64, _i64p, _i64p, _f64p, _f64p]
+    f(indptr.size - 1, dense.shape[1], indptr, indices, dense, out)
+    return out
+
+
+def spmm_cc_csr_f32(rowptr, colind, val, B):
+    rowptr, colind, val, B = _i32(rowptr), _i32(colind), _f32(val), _f32(B)
+    out = np.zeros((rowptr.size - 1, B.shape[1]), np.float32)
+    f = lib().oracle_spmm_cc_csr_f32
+    f.argtypes = [C.c_int, C.c_int, _i32p, _i32p, _f32p, _f32p, _f32p]
+    f(rowptr.size - 1, B.shape[1], rowptr, colind, val, B, out)
+    return out
+
+
+def bsrmm(bsr_rowptr, bsr_colind, bsr_val, bs, B, n, ldb, trans_b, direction=0, alpha=1.0,
+          beta=0.0, C0=None, ldc=None, c_layout=COL_MAJOR, kb=0):
+    """fp64-accumulated BSR SpMM -> float64 [mb*bs, n] (row-major)."""
+    bsr_rowptr, bsr_colind, bsr_val, B = _i32(bsr_rowptr), _i32(bsr_colind), _f32(bsr_val), _f32(B)
+    mb = bsr_rowptr.size - 1
+    m = mb * bs
+    if ldc is None:
+        ldc = m if c_layout == COL_MAJOR else n
+    out = np.zeros((m, n), np.float64)
+    c0 = None if C0 is None else _f32(C0)
+    f = lib().oracle_bsrmm_f64acc
+    f.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, _f32p, _i32p,
+                  _i32p, _f32p, C.c_int64, C.c_float, C.c_void_p, C.c_int64, C.c_int, _f64p]
+    f(direction, int(trans_b), mb, n, kb, bs, alpha, bsr_val.ravel(), bsr_rowptr, bsr_colind,
+      B.ravel(), ldb, beta, _opt(c0), ldc, c_layout, out)
+    return out
+
+
+def block_gemm(bsr_rowptr, bsr_colind, bsr_val, bs, Y, dim, Z0):
+    """block_cublas.cu:123-136 -> float64 [m, dim] (row-major view of col-major z)."""
+    bsr_rowptr, bsr_colind, bsr_val = _i32(bsr_rowptr), _i32(bsr_colind), _f32(bsr_val)
+    Y, Z0 = _f32(Y), _f32(Z0)
+    mb = bsr_rowptr.size - 1
+    out = np.zeros((mb * bs, dim), np.float64)
+    f = lib().oracle_block_gemm_f64acc
+    f.argtypes = [C.c_int, C.c_int, C.c_int, _i32p, _i32p, _f32p, _f32p, _f32p, _f64p]
+    f(mb, dim, bs, bsr_rowptr, bsr_colind, bsr_val.ravel(), Y.ravel(), Z0.ravel(), out)
+    return out
+
+
+def csr2bsr(rowptr, colind, val, m, n, bs, direction=0):
+    """-> (bsr_rowptr[mb+1], bsr_colind[nnzb], bsr_val[nnzb, bs, bs]) bit-exact contract."""
+    rowptr, colind, val = _i32(rowptr), _i32(colind), _f32(val)
+    mb = (m + bs - 1) // bs
+    brp = np.zeros(mb + 1, np.int32)
+    f = lib().oracle_csr2bsr_nnz
+    f.argtypes = [C.c_int, C.c_int, _i32p, _i32p, C.c_int, _i32p]
+    nnzb = int(f(m, n, rowptr, colind, bs, brp))
+    bci = np.zeros(max(nnzb, 1), np.int32)
+    bv = np.zeros(max(nnzb, 1) * bs * bs, np.float32)
+    g = lib().oracle_csr2bsr_fill
+    g.argtypes = [C.c_int, C.c_int, C.c_int, _i32p, _i32p, _f32p, C.c_int, _i32p, _i32p, _f32p]
+    g(direction, m, n, rowptr, colind, val, bs, brp, bci, bv)
+    return brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs)
+
+
+def bsr2csr(bsr_rowptr, bsr_colind, bsr_val, bs, direction=0):
+    bsr_rowptr, bsr_colind, bsr_val = _i32(bsr_rowptr), _i32(bsr_colind), _f32(bsr_val)
+    mb = bsr_rowptr.size - 1
+    nnz = int(bsr_rowptr[mb]) * bs * bs
+    rp = np.zeros(mb * bs + 1, np.int32)
+    ci = np.zeros(max(nnz, 1), np.int32)
+    v = np.zeros(max(nnz, 1), np.float32)
+    f = lib().oracle_bsr2csr
+    f.argtypes = [C.c_int, C.c_int, C.c_int, _i32p, _i32p, _f32p, C.c_int, _i32p, _i32p, _f32p]
+    f(direction, mb, 0, bsr_rowptr, bsr_colind, bsr_val.ravel(), bs, rp, ci, v)
+    return rp, ci[:nnz], v[:nnz]
+
+
+def permutate_csr(rowptr, colind, old2new):
+    rowptr, colind, old2new = _i32(rowptr), _i32(colind), _i32(old2new)
+    n = rowptr.size - 1
+    nrp = np.zeros(n + 1, np.int32)
+    nci = np.zeros(max(colind.size, 1), np.int32)
+    f = lib().oracle_permutate_csr
+    f.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p]
+    f(n, rowptr, colind, old2new, nrp, nci)
+    return nrp, nci[:colind.size]
+
+
+def calculate_nnzb(rowptr, colind, bs):
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    f = lib().oracle_calculate_nnzb
+    f.argtypes = [C.c_int, _i32p, _i32p, C.c_int]
+    return int(f(rowptr.size - 1, rowptr, colind, bs))
+
+
+def divide_matrix(rowptr, colind, bs, density):
+    """divide.cu:52-127 -> (csr_rowptr, csr_colind, bsr_rowptr, bsr_colind, bsr_val)."""
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    nb = (n + bs - 1) // bs
+    f = lib().oracle_divide_matrix
+    f.argtypes = [C.c_int, _i32p, _i32p, C.c_int, C.c_float] + [C.c_void_p] * 5 + [C.POINTER(C.c_int64)]
+    cnnz = C.c_int64(0)
+    nnzb = int(f(n, rowptr, colind, bs, density, None, None, None, None, None, C.byref(cnnz)))
+    crp = np.zeros(n + 1, np.int32)
+    cci = np.zeros(max(cnnz.value, 1), np.int32)
+    brp = np.zeros(nb + 1, np.int32)
+    bci = np.zeros(max(nnzb, 1), np.int32)
+    bv = np.zeros(max(nnzb, 1) * bs * bs, np.float32)
+    f(n, rowptr, colind, bs, density, crp.ctypes.data, cci.ctypes.data, brp.ctypes.data,
+      bci.ctypes.data, bv.ctypes.data, C.byref(cnnz))
+    return crp, cci[:cnnz.value], brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs)
+
+
+# --------------------------------------------------------------------------
+# The reference's own CPU code (oracle/_ref), when built.
+# --------------------------------------------------------------------------
+_ref_spmm = None
+_ref_host = None
+
+
+def ref_spmm_lib():
+    """libref_spmm.so = /root/reference/spmm.cc + matrix.h shim, or None."""
+    global _ref_spmm
+    p = os.path.join(HERE, "_ref", "libref_spmm.so")
+    if _ref_spmm is None and os.path.exists(p):
+        _ref_spmm = C.CDLL(p)
+    return _ref_spmm
+
+
+def ref_host_lib():
+    global _ref_host
+    p = os.path.join(HERE, "_ref", "libref_host.so")
+    if _ref_host is None and os.path.exists(p):
+        try:
+            _ref_host = C.CDLL(p)
+        except OSError:
+            _ref_host = None
+    return _ref_host
+
+
+def ref_csr_spmm(indptr, indices, dense, num_cols=None):
+    """The reference's csr_spmm (spmm.cc:7-25) itself: double, int64, unit weights."""
+    L = ref_spmm_lib()
+    indptr = np.ascontiguousarray(indptr, np.int64)
+    indices = np.ascontiguousarray(indices, np.int64)
+    dense = np.ascontiguousarray(dense, np.float64)
+    out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
+    L.ref_csr_spmm.argtypes = [C.c_int64, C.c_int64, C.c_int64, _i64p, _i64p, _f64p, _f64p]
+    L.ref_csr_spmm(indptr.size - 1, dense.shape[0] if num_cols is None else num_cols,
+                   dense.shape[1], indptr, indices, dense, out)
+    return out
+
+
+def ref_omp_threads():
+    L = ref_spmm_lib()
+    return int(L.ref_omp_max_threads()) if L is not None else 0
+
+
+def ref_calculate_nnzb(rowptr, colind, bs):
+    L = ref_host_lib()
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    L.ref_calculate_nnzb.argtypes = [C.c_int, _i32p, _i32p, C.c_int]
+    return int(L.ref_calculate_nnzb(rowptr.size - 1, rowptr, colind, bs))
+
+
+def ref_permutate(rowptr, colind, old2new):
+    L = ref_host_lib()
+    rowptr, colind, old2new = _i32(rowptr), _i32(colind), _i32(old2new)
+    n = rowptr.size - 1
+    nrp = np.zeros(n + 1, np.int32)
+    nci = np.zeros(max(colind.size, 1), np.int32)
+    L.ref_permutate.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p, _i32p]
+    L.ref_permutate(n, rowptr, colind, old2new, nrp, nci)
+    return nrp, nci[:colind.size]
+
+
+def ref_rcmk_graph(rowptr, colind):
+    L = ref_host_lib()
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    nrp = np.zeros(n + 1, np.int32)
+    nci = np.zeros(max(colind.size, 1), np.int32)
+    L.ref_rcmk_graph.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p]
+    L.ref_rcmk_graph(n, rowptr, colind, nrp, nci)
+    return nrp, nci[:colind.size]

@@ -1,0 +1,63 @@
+"""ctypes binding of libspmmdb.so (include/spmmdb.h).  Fails loudly when the
+library is missing -- the product never falls back to another implementation."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+c_i64 = C.c_int64
+vp = C.c_void_p
+
+
+class SpmmdbError(RuntimeError):
+    pass
+
+
+STATUS = {0: "OK", -1: "INVALID_VALUE", -2: "NOT_SUPPORTED", -3: "CUDA", -4: "ALLOC", -5: "ARCH"}
+
+# name -> argtypes; every symbol include/spmmdb.h declares
+SIGNATURES = {
+    "spmmdb_csrmm_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, c_i64, C.c_int, vp, c_i64, C.c_int,
+                         C.c_float, C.c_float, vp],
+    "spmmdb_csrmm_segment": [c_i64],
+    "spmmdb_bsrmm_f32": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_i64, C.c_int, C.c_float, vp, vp, vp, vp,
+                         c_i64, C.c_float, vp, c_i64, C.c_int, C.c_int, vp],
+    "spmmdb_block_gemm_f32": [C.c_int, C.c_int, c_i64, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp],
+    "spmmdb_csr2bsr_nnz": [C.c_int, C.c_int, vp, vp, C.c_int, vp, C.POINTER(C.c_int), vp],
+    "spmmdb_csr2bsr_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp],
+    "spmmdb_bsr2csr_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp],
+    "spmmdb_csrmm_host_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, vp, C.c_float, C.c_float, vp],
+    "spmmdb_version": [],
+    "spmmdb_last_error": [],
+    "spmmdb_device_sm": [],
+}
+
+
+def lib_path():
+    return os.path.join(HERE, "libspmmdb.so")
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise SpmmdbError(
+                f"{p} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(make -C spmm_denseblock_b200/csrc). There is no fallback path.")
+        L = C.CDLL(p)
+        for name, argtypes in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the ABI lost a symbol
+            fn.argtypes = argtypes
+            fn.restype = C.c_int
+        L.spmmdb_version.restype = C.c_char_p
+        L.spmmdb_last_error.restype = C.c_char_p
+        _LIB = L
+    return _LIB
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().spmmdb_last_error().decode() if rc == -3 else ""
+        raise SpmmdbError(f"{what} failed: {STATUS.get(rc, rc)} {msg}")

@@ -1,0 +1,326 @@
+// convert.cu -- csr2bsr (count + fill) and bsr2csr for sm_100a.  Integer /
+// byte-moving work, HBM-bound, bit-exact.  Replaces the cuSPARSE calls at
+// run_bsrmm.cu:121-142 (cusparseXcsr2bsrNnz + cusparseScsr2bsr) and
+// bsr2csr.cu:186-188 (cusparseSbsr2csr); CPU twins in the reference:
+// utility.cc:47-69 (calculateNnzb), divide.cu:52-127, my_run_bsr.cu:62-115.
+//
+// csr2bsr: one warp per block row runs a bs-way merge over the (ascending)
+// rows of the block row.  Lane l walks row l (and l+32, ... when bs > 32); the
+// warp minimum of the lanes' current column-block ids is the next non-zero
+// block, emitted in ascending order with no sort, no hash and no bound on the
+// number of column blocks.  The count pass and the fill pass are the same
+// walk; the fill pass assembles each bs x bs block in shared memory and writes
+// it out once, fully coalesced (zeros included), so bsr_val is written exactly
+// once and never pre-cleared.
+#include <limits.h>
+
+#include "common.cuh"
+
+namespace spmmdb {
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+
+__device__ __forceinline__ int warp_min(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// MODE 0: count blocks per block row -> counts[ib]
+// MODE 1: fill through a shared-memory tile (bs*bs floats per warp)
+// MODE 2: fill by direct scatter into pre-zeroed bsr_val (very large blocks)
+template <int R, int MODE>
+__global__ void __launch_bounds__(kWarpsPerCta * 32) csr2bsr_kernel(
+    int dir, int m, int mb, int bs, const int* __restrict__ rowptr, const int* __restrict__ colind,
+    const float* __restrict__ val, int* __restrict__ counts, const int* __restrict__ bsr_rowptr,
+    int* __restrict__ bsr_colind, float* __restrict__ bsr_val, int warps_per_cta) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31;
+  const int wid = threadIdx.x >> 5;
+  if (wid >= warps_per_cta) return;
+  const int bs2 = bs * bs;
+  float* tile = smem + (size_t)wid * bs2;
+  if (MODE == 1) {
+    for (int i = lane; i < bs2; i += 32) tile[i] = 0.f;
+    __syncwarp();
+  }
+  for (int ib = blockIdx.x * warps_per_cta + wid; ib < mb; ib += gridDim.x * warps_per_cta) {
+    int p[R], e[R], col[R], head[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) {
+      const int r = lane + 32 * t;
+      const int row = ib * bs + r;
+      p[t] = 0; e[t] = 0;
+      if (r < bs && row < m) { p[t] = __ldg(rowptr + row); e[t] = __ldg(rowptr + row + 1); }
+      col[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) : -1;
+      head[t] = (col[t] >= 0) ? col[t] / bs : INT_MAX;
+    }
+    const int64_t base = (MODE == 0) ? 0 : __ldg(bsr_rowptr + ib);
+    int step = 0;
+    while (true) {
+      int mymin = head[0];
+#pragma unroll
+      for (int t = 1; t < R; ++t) mymin = min(mymin, head[t]);
+      const int bmin = warp_min(mymin);
+      if (bmin == INT_MAX) break;
+      const int col0 = bmin * bs;
+      float* out = (MODE == 0) ? nullptr : bsr_val + (base + step) * bs2;
+#pragma unroll
+      for (int t = 0; t < R; ++t) {
+        const int r = lane + 32 * t;
+        while (head[t] == bmin) {
+          if (MODE != 0) {
+            const int c = col[t] - col0;
+            const float v = __ldg(val + p[t]);
+            const int off = (dir == SPMMDB_DIR_ROW) ? r * bs + c : c * bs + r;
+            if (MODE == 1) tile[off] = v; else out[off] = v;
+          }
+          ++p[t];
+          col[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) : -1;
+          head[t] = (col[t] >= 0) ? col[t] / bs : INT_MAX;
+        }
+      }
+      if (MODE == 1) {
+        __syncwarp();
+        if ((bs2 & 3) == 0) {
+          float4* o4 = reinterpret_cast<float4*>(out);
+          float4* t4 = reinterpret_cast<float4*>(tile);
+          for (int i = lane; i < bs2 / 4; i += 32) {
+            __stcs(o4 + i, t4[i]);
+            t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        } else {
+          for (int i = lane; i < bs2; i += 32) { out[i] = tile[i]; tile[i] = 0.f; }
+        }
+        __syncwarp();
+      }
+      if (MODE != 0 && lane == 0) bsr_colind[base + step] = bmin;
+      ++step;
+    }
+    if (MODE == 0 && lane == 0) counts[ib] = step;
+  }
+}
+
+// ---- exclusive scan of counts[n] -> out[n+1] (three small kernels) ----------
+constexpr int kScanTile = 2048;  // elements per CTA (256 threads x 8)
+
+__device__ __forceinline__ int block_exclusive_scan_256(int v, int* total) {
+  __shared__ int warp_sums[8];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_sums[wid] = inc;
+  __syncthreads();
+  if (wid == 0) {
+    int w = (lane < 8) ? warp_sums[lane] : 0;
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, w, o);
+      if (lane >= o) w += t;
+    }
+    if (lane < 8) warp_sums[lane] = w;
+  }
+  __syncthreads();
+  const int woff = (wid == 0) ? 0 : warp_sums[wid - 1];
+  *total = warp_sums[7];
+  __syncthreads();
+  return woff + inc - v;
+}
+
+__global__ void __launch_bounds__(256) scan_tile_sums(const int* __restrict__ in, int n, int* __restrict__ sums) {
+  const int base = blockIdx.x * kScanTile + threadIdx.x * 8;
+  int s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) if (base + i < n) s += in[base + i];
+  int total;
+  block_exclusive_scan_256(s, &total);
+  if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(256) scan_sums_inplace(int* sums, int ntiles) {
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < ntiles; base += 256) {
+    const int i = base + threadIdx.x;
+    const int v = (i < ntiles) ? sums[i] : 0;
+    int total;
+    const int ex = block_exclusive_scan_256(v, &total);
+    if (i < ntiles) sums[i] = carry + ex;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += total;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) scan_apply(const int* __restrict__ in, int n, const int* __restrict__ sums,
+                                                  int* __restrict__ out) {
+  const int base = blockIdx.x * kScanTile + threadIdx.x * 8;
+  int v[8], s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { v[i] = (base + i < n) ? in[base + i] : 0; s += v[i]; }
+  int total;
+  int ex = block_exclusive_scan_256(s, &total) + sums[blockIdx.x];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    if (base + i < n) out[base + i] = ex;
+    ex += v[i];
+    if (base + i == n - 1) out[n] = ex;
+  }
+}
+
+// ---- bsr2csr ------------------------------------------------------------------
+// One warp per non-zero block.  Lane 0 finds the block row with a binary search
+// over bsr_rowptr; the warp then reads the block contiguously and writes each of
+// its bs row pieces to its closed-form position.
+__global__ void __launch_bounds__(256) bsr2csr_kernel(int dir, int mb, int bs, const int* __restrict__ bsr_rowptr,
+                                                      const int* __restrict__ bsr_colind,
+                                                      const float* __restrict__ bsr_val, int* __restrict__ csr_rowptr,
+                                                      int* __restrict__ csr_colind, float* __restrict__ csr_val) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int nnzb = __ldg(bsr_rowptr + mb);
+  const int bs2 = bs * bs;
+  // row pointer: closed form, one thread per CSR row
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row <= (int64_t)mb * bs;
+       row += (int64_t)gridDim.x * blockDim.x) {
+    if (row == (int64_t)mb * bs) { csr_rowptr[row] = nnzb * bs2; break; }
+    const int ib = (int)(row / bs), r = (int)(row % bs);
+    const int b0 = __ldg(bsr_rowptr + ib), cnt = __ldg(bsr_rowptr + ib + 1) - b0;
+    csr_rowptr[row] = b0 * bs2 + r * cnt * bs;
+  }
+  for (int64_t p = warp; p < nnzb; p += nwarps) {
+    int ib = 0;
+    if (lane == 0) {
+      int lo = 0, hi = mb;  // largest ib with bsr_rowptr[ib] <= p
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(bsr_rowptr + mid) <= p) lo = mid; else hi = mid;
+      }
+      ib = lo;
+    }
+    ib = __shfl_sync(0xffffffffu, ib, 0);
+    const int64_t b0 = __ldg(bsr_rowptr + ib), cnt = __ldg(bsr_rowptr + ib + 1) - b0;
+    const int64_t q = p - b0;
+    const int col0 = __ldg(bsr_colind + p) * bs;
+    const float* __restrict__ blk = bsr_val + p * bs2;
+    const int64_t out0 = b0 * bs2 + q * bs;
+    for (int e = lane; e < bs2; e += 32) {
+      const int r = e / bs, c = e - r * bs;
+      const float v = (dir == SPMMDB_DIR_ROW) ? __ldcs(blk + e) : __ldcs(blk + c * bs + r);
+      const int64_t o = out0 + (int64_t)r * cnt * bs + c;
+      __stcs(csr_colind + o, col0 + c);
+      __stcs(csr_val + o, v);
+    }
+  }
+}
+
+template <int MODE>
+int launch_csr2bsr(int dir, int m, int mb, int bs, const int* rowptr, const int* colind, const float* val,
+                   int* counts, const int* bsr_rowptr, int* bsr_colind, float* bsr_val, cudaStream_t st) {
+  const int R = (bs + 31) / 32;
+  int wpc = kWarpsPerCta;
+  size_t smem = 0;
+  if (MODE == 1) {
+    const size_t per_warp = sizeof(float) * (size_t)bs * bs;
+    while (wpc > 1 && per_warp * wpc > 200 * 1024) wpc >>= 1;
+    smem = per_warp * wpc;
+  }
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  const int64_t want = ((int64_t)mb + wpc - 1) / wpc;
+  const int grid = (int)(want < (int64_t)nsm * 16 ? (want > 0 ? want : 1) : (int64_t)nsm * 16);
+#define SPMMDB_LAUNCH_C2B(RR)                                                                                   \
+  do {                                                                                                          \
+    if (smem > 48 * 1024)                                                                                       \
+      SPMMDB_CUDA_OK(cudaFuncSetAttribute(csr2bsr_kernel<RR, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                          (int)smem));                                                          \
+    csr2bsr_kernel<RR, MODE><<<grid, kWarpsPerCta * 32, smem, st>>>(dir, m, mb, bs, rowptr, colind, val, counts, \
+                                                                    bsr_rowptr, bsr_colind, bsr_val, wpc);      \
+  } while (0)
+  if (R <= 1) SPMMDB_LAUNCH_C2B(1);
+  else if (R <= 2) SPMMDB_LAUNCH_C2B(2);
+  else if (R <= 4) SPMMDB_LAUNCH_C2B(4);
+  else SPMMDB_LAUNCH_C2B(8);
+#undef SPMMDB_LAUNCH_C2B
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
+}  // namespace
+}  // namespace spmmdb
+
+using namespace spmmdb;
+
+extern "C" int spmmdb_csr2bsr_nnz(int m, int n, const int* rowptr, const int* colind, int block_dim,
+                                  int* bsr_rowptr, int* nnzb_host, void* stream) {
+  if (m < 0 || n < 0 || block_dim <= 0 || block_dim > 256) return SPMMDB_ERR_INVALID_VALUE;
+  if (bsr_rowptr == nullptr || nnzb_host == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int mb = (m + block_dim - 1) / block_dim;
+  if (mb == 0) {
+    SPMMDB_CUDA_OK(cudaMemsetAsync(bsr_rowptr, 0, sizeof(int), st));
+    SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+    *nnzb_host = 0;
+    return SPMMDB_OK;
+  }
+  if (rowptr == nullptr || (colind == nullptr && m > 0)) return SPMMDB_ERR_INVALID_VALUE;
+  const int ntiles = (mb + kScanTile - 1) / kScanTile;
+  int* ws = (int*)scratch(kScratchConvert, sizeof(int) * ((size_t)mb + ntiles + 8), st);
+  if (ws == nullptr) return SPMMDB_ERR_ALLOC;
+  int* counts = ws;
+  int* sums = ws + mb;
+  int rc = launch_csr2bsr<0>(SPMMDB_DIR_ROW, m, mb, block_dim, rowptr, colind, nullptr, counts, nullptr, nullptr,
+                             nullptr, st);
+  if (rc != SPMMDB_OK) return rc;
+  scan_tile_sums<<<ntiles, 256, 0, st>>>(counts, mb, sums);
+  scan_sums_inplace<<<1, 256, 0, st>>>(sums, ntiles);
+  scan_apply<<<ntiles, 256, 0, st>>>(counts, mb, sums, bsr_rowptr);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(nnzb_host, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  return SPMMDB_OK;
+}
+
+extern "C" int spmmdb_csr2bsr_f32(int dir, int m, int n, const int* rowptr, const int* colind, const float* val,
+                                  int block_dim, const int* bsr_rowptr, int* bsr_colind, float* bsr_val,
+                                  void* stream) {
+  if (m < 0 || n < 0 || block_dim <= 0 || block_dim > 256) return SPMMDB_ERR_INVALID_VALUE;
+  if (dir != SPMMDB_DIR_ROW && dir != SPMMDB_DIR_COLUMN) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  const int mb = (m + block_dim - 1) / block_dim;
+  if (mb == 0) return SPMMDB_OK;
+  if (rowptr == nullptr || colind == nullptr || val == nullptr || bsr_rowptr == nullptr || bsr_colind == nullptr ||
+      bsr_val == nullptr)
+    return SPMMDB_ERR_INVALID_VALUE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (block_dim <= 128)
+    return launch_csr2bsr<1>(dir, m, mb, block_dim, rowptr, colind, val, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);
+  // very large blocks: clear + scatter (needs nnzb: read it back)
+  int nnzb = 0;
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(&nnzb, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  SPMMDB_CUDA_OK(cudaMemsetAsync(bsr_val, 0, sizeof(float) * (size_t)nnzb * block_dim * block_dim, st));
+  return launch_csr2bsr<2>(dir, m, mb, block_dim, rowptr, colind, val, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);
+}
+
+extern "C" int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr, const int* bsr_colind,
+                                  const float* bsr_val, int block_dim, int* csr_rowptr, int* csr_colind,
+                                  float* csr_val, void* stream) {
+  if (mb < 0 || nb < 0 || block_dim <= 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (dir != SPMMDB_DIR_ROW && dir != SPMMDB_DIR_COLUMN) return SPMMDB_ERR_INVALID_VALUE;
+  if (bsr_rowptr == nullptr || csr_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  bsr2csr_kernel<<<nsm * 8, 256, 0, st>>>(dir, mb, block_dim, bsr_rowptr, bsr_colind, bsr_val, csr_rowptr,
+                                          csr_colind, csr_val);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}

@@ -1,0 +1,333 @@
+// csrmm.cu -- CSR x dense (fp32) for sm_100a.  HBM/L2-bandwidth-bound gather:
+// no tensor cores.  Replaces gespmm_csrmm.h:95-166 (spmm_test2) and the
+// cuSPARSE csrmm / csrmm2 call sites (run_csrmm.cu:133-142).
+//
+// Mapping: one "group" of LPR lanes owns one row segment; every lane owns VEC
+// vectors (float4 when 16-byte aligned, else float) of the output row, so a
+// B-row gather is one fully coalesced LPR*16-byte request and the (col, val)
+// pairs are read once, coalesced, and broadcast with warp shuffles.  U*VEC
+// independent 16-byte loads are in flight per lane before the FMAs retire them
+// in CSR order, so each output element is the same fp32 FMA chain as the
+// reference kernel (bit-exact) while the memory system sees deep MLP.
+//
+// Rows longer than `seg` non-zeros are cut into row-relative segments of `seg`
+// non-zeros: the main kernel queues them, the long-row kernel computes one
+// partial per segment and the group that finishes a row's last segment adds
+// the partials in segment order.  The split depends only on the row, so the
+// result is deterministic and independent of any row sharding.
+#include "common.cuh"
+
+namespace spmmdb {
+namespace {
+
+struct LongRow { int row; int seg_base; int nseg; int epoch; };
+
+struct CsrArgs {
+  int m, K;
+  const int* rowptr;
+  const int* colind;
+  const float* val;
+  const float* B;
+  int64_t ldb;
+  float* C;
+  int64_t ldc;
+  float alpha, beta;
+  int seg;              // row segment length (power of two)
+  // long-row queue (scratch)
+  int* counters;        // [0] = long rows, [1] = segments, [2] = overflow flag
+  LongRow* long_rows;   // capacity cap_rows
+  int* seg_owner;       // capacity cap_segs: segment -> long row slot
+  int* done;            // capacity cap_rows, zero between calls
+  float* partial;       // capacity cap_segs * Kpad floats
+  int cap_rows, cap_segs;
+  int Kpad;             // K rounded up to 4
+  int epoch;            // call counter: tells this call's queue entries from stale ones
+};
+
+template <typename V> struct VecOps;
+template <> struct VecOps<float4> {
+  static constexpr int W = 4;
+  __device__ static float4 zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ static void fma(float4& a, float v, const float4& b) {
+    a.x = fmaf(v, b.x, a.x); a.y = fmaf(v, b.y, a.y); a.z = fmaf(v, b.z, a.z); a.w = fmaf(v, b.w, a.w);
+  }
+  __device__ static void add(float4& a, const float4& b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+  __device__ static float4 axpby(float al, const float4& a, float be, const float4& c) {
+    return make_float4(fmaf(be, c.x, al * a.x), fmaf(be, c.y, al * a.y), fmaf(be, c.z, al * a.z), fmaf(be, c.w, al * a.w));
+  }
+  __device__ static float4 scale(float al, const float4& a) { return make_float4(al * a.x, al * a.y, al * a.z, al * a.w); }
+};
+template <> struct VecOps<float> {
+  static constexpr int W = 1;
+  __device__ static float zero() { return 0.f; }
+  __device__ static void fma(float& a, float v, const float& b) { a = fmaf(v, b, a); }
+  __device__ static void add(float& a, const float& b) { a += b; }
+  __device__ static float axpby(float al, const float& a, float be, const float& c) { return fmaf(be, c, al * a); }
+  __device__ static float scale(float al, const float& a) { return al * a; }
+};
+
+// Accumulate one row segment [lb, hb) into acc[VEC].  Must be called by all 32
+// lanes of the warp (shuffles); groups whose range is empty idle.
+// nvec = number of V-vectors per row of B that this column tile covers,
+// vbase = first vector index of the tile.
+template <typename V, int LPR, int VEC, int U>
+__device__ __forceinline__ void accumulate_segment(const CsrArgs& a, int lb, int hb, int sub, int grp,
+                                                   int vbase, int nvec, V (&acc)[VEC]) {
+  using Ops = VecOps<V>;
+  const V* __restrict__ Bv = reinterpret_cast<const V*>(a.B);
+  const int64_t ldbv = a.ldb / Ops::W;
+  bool colok[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) colok[i] = (sub + i * LPR) < nvec;
+
+  for (int base = lb; __any_sync(0xffffffffu, base < hb); base += LPR) {
+    const int idx = base + sub;
+    int c = 0;
+    float v = 0.f;
+    if (idx < hb) {
+      c = __ldg(a.colind + idx);
+      v = __ldg(a.val + idx);
+    }
+    const int cnt = hb - base;  // entries of this group's chunk (may be <= 0 or > LPR)
+#pragma unroll 1
+    for (int kk = 0; kk < LPR; kk += U) {
+      if (__all_sync(0xffffffffu, kk >= cnt)) break;
+      V b[U][VEC];
+      float vv[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int src = grp * LPR + kk + u;
+        const int cc = __shfl_sync(0xffffffffu, c, src);
+        vv[u] = __shfl_sync(0xffffffffu, v, src);
+        const V* __restrict__ brow = Bv + (int64_t)cc * ldbv + vbase + sub;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+          if (kk + u < cnt && colok[i]) b[u][i] = __ldg(brow + i * LPR);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (kk + u < cnt) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) {
+            if (colok[i]) Ops::fma(acc[i], vv[u], b[u][i]);
+          }
+        }
+      }
+    }
+  }
+}
+
+template <typename V, int LPR, int VEC>
+__device__ __forceinline__ void store_row(const CsrArgs& a, int row, int sub, int vbase, int nvec,
+                                          const V (&acc)[VEC]) {
+  using Ops = VecOps<V>;
+  V* __restrict__ Cv = reinterpret_cast<V*>(a.C) + (int64_t)row * (a.ldc / Ops::W) + vbase + sub;
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) {
+    if (sub + i * LPR < nvec) {
+      V out;
+      if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[i * LPR]);
+      else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i]);
+      else out = acc[i];
+      __stcs(Cv + i * LPR, out);
+    }
+  }
+}
+
+// Main kernel: one group (LPR lanes) per row.  K > 32 lanes * VEC vectors is
+// covered by looping over column tiles inside the kernel.
+template <typename V, int LPR, int VEC, int U>
+__global__ void __launch_bounds__(256) csrmm_rows_kernel(const CsrArgs a) {
+  constexpr int GPW = 32 / LPR;
+  using Ops = VecOps<V>;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPR, grp = lane / LPR;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t row64 = warp * GPW + grp;
+  const int nvec_total = (a.K + Ops::W - 1) / Ops::W;
+
+  const bool valid = row64 < a.m;
+  const int row = valid ? (int)row64 : 0;
+  int lb = 0, hb = 0;
+  if (valid) {
+    lb = __ldg(a.rowptr + row);
+    hb = __ldg(a.rowptr + row + 1);
+  }
+  // Long row: hand it to the long-row kernel.  If the queue is full (caller
+  // passed a too small nnz) the row is processed here, slowly but correctly.
+  const bool is_long = (hb - lb) > a.seg;
+  const int nseg = is_long ? (hb - lb + a.seg - 1) / a.seg : 0;
+  int slot = -1, seg_base = 0;
+  if (is_long && sub == 0) {
+    slot = atomicAdd(a.counters + 0, 1);
+    seg_base = atomicAdd(a.counters + 1, nseg);
+    if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
+      atomicExch(a.counters + 2, 1);
+      slot = -1;
+    } else {
+      a.long_rows[slot] = LongRow{row, seg_base, nseg, a.epoch};
+    }
+  }
+  slot = __shfl_sync(0xffffffffu, slot, grp * LPR);
+  seg_base = __shfl_sync(0xffffffffu, seg_base, grp * LPR);
+  const bool queued = is_long && slot >= 0;
+  if (queued) {
+    for (int s = sub; s < nseg; s += LPR) a.seg_owner[seg_base + s] = slot;
+    hb = lb;
+  }
+
+  for (int vbase = 0; vbase < nvec_total; vbase += LPR * VEC) {
+    const int nvec = min(LPR * VEC, nvec_total - vbase);
+    V acc[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+    accumulate_segment<V, LPR, VEC, U>(a, lb, hb, sub, grp, vbase, nvec, acc);
+    if (valid && !queued) store_row<V, LPR, VEC>(a, row, sub, vbase, nvec, acc);
+  }
+}
+
+// Long-row kernel: one group per queued segment (all column tiles), partial
+// sums to scratch, last finisher of a row reduces them in segment order.
+template <typename V, int LPR, int VEC, int U>
+__global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
+  constexpr int GPW = 32 / LPR;
+  using Ops = VecOps<V>;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPR, grp = lane / LPR;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int nseg_total = min(*(volatile int*)(a.counters + 1), a.cap_segs);
+  const int nvec_total = (a.K + Ops::W - 1) / Ops::W;
+  const int kpadv = a.Kpad / Ops::W;
+  V* __restrict__ Pv = reinterpret_cast<V*>(a.partial);
+
+  for (int64_t item0 = warp * GPW; item0 < nseg_total; item0 += nwarps * GPW) {
+    const int64_t item = item0 + grp;
+    bool valid = item < nseg_total;
+    int slot = 0;
+    LongRow lr = LongRow{0, 0, 0, 0};
+    int lb = 0, hb = 0;
+    if (valid) {
+      slot = a.seg_owner[item];
+      valid = slot >= 0 && slot < a.cap_rows;
+      if (valid) {
+        lr = a.long_rows[slot];
+        // entries left over from an overflowed / earlier queue fail this test
+        valid = lr.epoch == a.epoch && item >= lr.seg_base && item < (int64_t)lr.seg_base + lr.nseg;
+      }
+    }
+    if (valid) {
+      const int s = (int)item - lr.seg_base;
+      const int row_lb = __ldg(a.rowptr + lr.row);
+      const int row_hb = __ldg(a.rowptr + lr.row + 1);
+      lb = row_lb + s * a.seg;
+      hb = min(row_hb, lb + a.seg);
+    }
+    for (int vbase = 0; vbase < nvec_total; vbase += LPR * VEC) {
+      const int nvec = min(LPR * VEC, nvec_total - vbase);
+      V acc[VEC];
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+      accumulate_segment<V, LPR, VEC, U>(a, lb, hb, sub, grp, vbase, nvec, acc);
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+          if (sub + i * LPR < nvec) Pv[item * kpadv + vbase + sub + i * LPR] = acc[i];
+      }
+    }
+    // publish, then let the last finisher of the row reduce in segment order
+    __threadfence();
+    __syncwarp();
+    int last = 0;
+    if (valid && sub == 0) last = (atomicAdd(a.done + slot, 1) == lr.nseg - 1);
+    last = __shfl_sync(0xffffffffu, last, grp * LPR);
+    if (last) {
+      __threadfence();
+      if (sub == 0) a.done[slot] = 0;
+      for (int vbase = 0; vbase < nvec_total; vbase += LPR * VEC) {
+        const int nvec = min(LPR * VEC, nvec_total - vbase);
+        V acc[VEC];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+        for (int s = 0; s < lr.nseg; ++s) {
+          const V* __restrict__ p = Pv + (int64_t)(lr.seg_base + s) * kpadv + vbase + sub;
+#pragma unroll
+          for (int i = 0; i < VEC; ++i)
+            if (sub + i * LPR < nvec) {
+              if (s == 0) acc[i] = __ldcg(p + i * LPR); else Ops::add(acc[i], __ldcg(p + i * LPR));
+            }
+        }
+        store_row<V, LPR, VEC>(a, lr.row, sub, vbase, nvec, acc);
+      }
+    }
+  }
+}
+
+template <typename V, int LPR, int VEC, int U>
+int launch_variant(const CsrArgs& a, int long_ctas, cudaStream_t st) {
+  constexpr int GPW = 32 / LPR;
+  const int rows_per_cta = 8 * GPW;
+  dim3 grid((unsigned)((a.m + rows_per_cta - 1) / rows_per_cta));
+  csrmm_rows_kernel<V, LPR, VEC, U><<<grid, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  csrmm_long_kernel<V, LPR, VEC, U><<<long_ctas, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
+template <typename V>
+int dispatch(const CsrArgs& a, int long_ctas, cudaStream_t st) {
+  const int nvec = (a.K + VecOps<V>::W - 1) / VecOps<V>::W;
+  if (nvec <= 4) return launch_variant<V, 4, 1, 4>(a, long_ctas, st);
+  if (nvec <= 8) return launch_variant<V, 8, 1, 8>(a, long_ctas, st);
+  if (nvec <= 16) return launch_variant<V, 16, 1, 8>(a, long_ctas, st);
+  if (nvec <= 32) return launch_variant<V, 32, 1, 8>(a, long_ctas, st);
+  if (nvec <= 64) return launch_variant<V, 32, 2, 8>(a, long_ctas, st);
+  if (nvec <= 96) return launch_variant<V, 32, 3, 4>(a, long_ctas, st);
+  return launch_variant<V, 32, 4, 4>(a, long_ctas, st);
+}
+
+}  // namespace
+
+// Core entry: row-major B and C.
+int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* colind, const float* val,
+                   const float* B, int64_t ldb, float* C, int64_t ldc, float alpha, float beta,
+                   cudaStream_t st) {
+  CsrArgs a;
+  a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
+  a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
+  a.seg = spmmdb_csrmm_segment(nnz);
+  a.Kpad = (K + 3) & ~3;
+  static int g_epoch = 0;
+  a.epoch = ++g_epoch;
+  // worst case: every segment queued.  segments <= nnz/seg + long rows, long rows <= nnz/seg
+  const int64_t max_long = nnz / a.seg + 1;
+  const int64_t max_segs = 2 * max_long;
+  a.cap_rows = (int)max_long;
+  a.cap_segs = (int)max_segs;
+  const size_t hdr = 64;
+  const size_t bytes_q = hdr + sizeof(LongRow) * max_long + sizeof(int) * max_segs + sizeof(int) * max_long;
+  char* q = (char*)scratch(kScratchCsrLong, bytes_q, st);
+  float* part = (float*)scratch(kScratchCsrPartial, sizeof(float) * (size_t)max_segs * a.Kpad, st);
+  if (q == nullptr || part == nullptr) return SPMMDB_ERR_ALLOC;
+  a.counters = (int*)q;
+  a.long_rows = (LongRow*)(q + hdr);
+  a.seg_owner = (int*)(q + hdr + sizeof(LongRow) * max_long);
+  a.done = a.seg_owner + max_segs;
+  a.partial = part;
+  SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 16, st));
+  const int nsm = device_num_sms();
+  const int long_ctas = (nsm > 0 ? nsm : 148) * 2;
+  const bool vec4 = (K % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
+                    (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
+  return vec4 ? dispatch<float4>(a, long_ctas, st) : dispatch<float>(a, long_ctas, st);
+}
+
+}  // namespace spmmdb
+
+extern "C" int spmmdb_csrmm_segment(int64_t nnz) {
+  if (nnz < (int64_t)4 << 20) return 64;
+  if (nnz < (int64_t)32 << 20) return 256;
+  return 1024;
+}

@@ -1,0 +1,125 @@
+"""Host-side mirror of the reference's operator interface for the hot path,
+on torch CUDA tensors (device memory + streams only; all arithmetic happens in
+libspmmdb.so).  Names and argument meaning follow the reference:
+gespmm_csrmm (gespmm_csrmm.h:422-426), rocsparse_bsrmm_template
+(rocsparse_bsrmm.h:102-108), cusparseXcsr2bsrNnz / cusparseScsr2bsr
+(run_bsrmm.cu:121-142), cusparseSbsr2csr (bsr2csr.cu:186-188), the per-block
+GEMM loop of block_cublas.cu:123-136."""
+import ctypes as C
+
+import torch
+
+from ._lib import lib, check
+
+ROW_MAJOR, COL_MAJOR = 0, 1
+DIR_ROW, DIR_COLUMN = 0, 1
+MATH_FP32, MATH_TF32, MATH_BF16 = 0, 1, 2
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)
+
+
+def _dev(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("spmmdb ops take CUDA tensors (there is no CPU path)")
+        if t is not None and not t.is_contiguous():
+            raise ValueError("spmmdb ops take contiguous tensors")
+
+
+def csrmm_segment(nnz):
+    return lib().spmmdb_csrmm_segment(int(nnz))
+
+
+def csrmm(rowptr, colind, val, B, C_out, m, k, K, ldb=None, b_layout=ROW_MAJOR, ldc=None, c_layout=ROW_MAJOR,
+          alpha=1.0, beta=0.0, nnz=None):
+    """C = alpha*A*B + beta*C with explicit layouts (spmmdb_csrmm_f32)."""
+    _dev(rowptr, colind, val, B, C_out)
+    if ldb is None:
+        ldb = K if b_layout == ROW_MAJOR else k
+    if ldc is None:
+        ldc = K if c_layout == ROW_MAJOR else m
+    nnz = colind.numel() if nnz is None else nnz
+    rc = lib().spmmdb_csrmm_f32(m, k, K, nnz, _p(rowptr), _p(colind), _p(val), _p(B), ldb, b_layout, _p(C_out), ldc,
+                                c_layout, alpha, beta, _stream())
+    check(rc, "spmmdb_csrmm_f32")
+    return C_out
+
+
+def gespmm_csrmm(A_nrows, B_ncols, A_rowPtr, A_colInd, A_val, B, C_out):
+    """gespmm_csrmm<float>(A_nrows, B_ncols, rowPtr, colInd, val, B, C): row-major B/C,
+    alpha=1, beta=0, nnz unknown to the callee (gespmm_csrmm.h:422-426)."""
+    _dev(A_rowPtr, A_colInd, A_val, B, C_out)
+    k = B.numel() // max(B_ncols, 1)
+    rc = lib().spmmdb_csrmm_f32(A_nrows, k, B_ncols, -1, _p(A_rowPtr), _p(A_colInd), _p(A_val), _p(B), B_ncols,
+                                ROW_MAJOR, _p(C_out), B_ncols, ROW_MAJOR, 1.0, 0.0, _stream())
+    check(rc, "gespmm_csrmm")
+    return C_out
+
+
+def bsrmm(direction, trans_b, mb, n, kb, nnzb, alpha, bsr_val, bsr_rowptr, bsr_colind, block_dim, B, ldb, beta,
+          C_out, ldc, c_layout=COL_MAJOR, math=MATH_FP32):
+    _dev(bsr_val, bsr_rowptr, bsr_colind, B, C_out)
+    rc = lib().spmmdb_bsrmm_f32(direction, int(trans_b), mb, n, kb, nnzb, block_dim, alpha, _p(bsr_val),
+                                _p(bsr_rowptr), _p(bsr_colind), _p(B), ldb, beta, _p(C_out), ldc, c_layout, math,
+                                _stream())
+    check(rc, "spmmdb_bsrmm_f32")
+    return C_out
+
+
+def rocsparse_bsrmm(direction, trans_A, trans_B, mb, n, kb, nnzb, alpha, bsr_val, bsr_row_ptr, bsr_col_ind,
+                    block_dim, B, ldb, beta, C_out, ldc, math=MATH_FP32):
+    """rocsparse_bsrmm_template<float> argument order (rocsparse_bsrmm.h:102-108); returns the
+    status code instead of raising, like the reference (0 = CUSPARSE_STATUS_SUCCESS)."""
+    if trans_A != 0:
+        return -2  # CUSPARSE_STATUS_MATRIX_TYPE_NOT_SUPPORTED (rocsparse_bsrmm.h:139-141)
+    return lib().spmmdb_bsrmm_f32(direction, int(trans_B), mb, n, kb, nnzb, block_dim, alpha, _p(bsr_val),
+                                  _p(bsr_row_ptr), _p(bsr_col_ind), _p(B), ldb, beta, _p(C_out), ldc, COL_MAJOR,
+                                  math, _stream())
+
+
+def block_gemm(mb, dim, nnzb, block_dim, bsr_rowptr, bsr_colind, bsr_val, Y, Z, math=MATH_FP32):
+    _dev(bsr_rowptr, bsr_colind, bsr_val, Y, Z)
+    rc = lib().spmmdb_block_gemm_f32(mb, dim, nnzb, block_dim, _p(bsr_rowptr), _p(bsr_colind), _p(bsr_val), _p(Y),
+                                     _p(Z), math, _stream())
+    check(rc, "spmmdb_block_gemm_f32")
+    return Z
+
+
+def csr2bsr_nnz(m, n, rowptr, colind, block_dim, bsr_rowptr):
+    _dev(rowptr, colind, bsr_rowptr)
+    nnzb = C.c_int(0)
+    rc = lib().spmmdb_csr2bsr_nnz(m, n, _p(rowptr), _p(colind), block_dim, _p(bsr_rowptr), C.byref(nnzb), _stream())
+    check(rc, "spmmdb_csr2bsr_nnz")
+    return nnzb.value
+
+
+def csr2bsr(m, n, rowptr, colind, val, block_dim, direction=DIR_ROW):
+    """Both phases, allocating the outputs between them like run_bsrmm.cu:121-142."""
+    mb = (m + block_dim - 1) // block_dim
+    bsr_rowptr = torch.empty(mb + 1, dtype=torch.int32, device=rowptr.device)
+    nnzb = csr2bsr_nnz(m, n, rowptr, colind, block_dim, bsr_rowptr)
+    bsr_colind = torch.empty(nnzb, dtype=torch.int32, device=rowptr.device)
+    bsr_val = torch.empty(nnzb * block_dim * block_dim, dtype=torch.float32, device=rowptr.device)
+    rc = lib().spmmdb_csr2bsr_f32(direction, m, n, _p(rowptr), _p(colind), _p(val), block_dim, _p(bsr_rowptr),
+                                  _p(bsr_colind), _p(bsr_val), _stream())
+    check(rc, "spmmdb_csr2bsr_f32")
+    return bsr_rowptr, bsr_colind, bsr_val
+
+
+def bsr2csr(mb, nb, bsr_rowptr, bsr_colind, bsr_val, block_dim, direction=DIR_ROW):
+    _dev(bsr_rowptr, bsr_colind, bsr_val)
+    nnz = bsr_colind.numel() * block_dim * block_dim
+    dev = bsr_rowptr.device
+    csr_rowptr = torch.empty(mb * block_dim + 1, dtype=torch.int32, device=dev)
+    csr_colind = torch.empty(nnz, dtype=torch.int32, device=dev)
+    csr_val = torch.empty(nnz, dtype=torch.float32, device=dev)
+    rc = lib().spmmdb_bsr2csr_f32(direction, mb, nb, _p(bsr_rowptr), _p(bsr_colind), _p(bsr_val), block_dim,
+                                  _p(csr_rowptr), _p(csr_colind), _p(csr_val), _stream())
+    check(rc, "spmmdb_bsr2csr_f32")
+    return csr_rowptr, csr_colind, csr_val

@@ -1,0 +1,284 @@
+"""GPU parity tests: every call goes through the C ABI (libspmmdb.so) and is compared with
+the CPU oracle on the same seeded inputs.  Bars (BASELINE.json north_star):
+  * csr2bsr / bsr2csr: bit-exact.
+  * fp32 CSR path: relative error <= 1e-5 against the fp64 oracle (error measured against
+    sum_j |a_ij b_jk|), and BIT-EXACT against the reference kernel's own fp32 FMA order for
+    rows no longer than one segment.
+  * fp32 BSR path: <= 1e-5; tf32/bf16 tensor-core BSR path: <= 1e-2.
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import random_bsr, random_csr
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-5
+TOL_TC = 1e-2
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import spmm_denseblock_b200 as p
+    assert torch.cuda.is_available()
+    p.lib()
+    return p
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def err_vs(oracle, got, ref64, rp, ci, v, Bm, K, **kw):
+    scale = oracle.csrmm(rp, ci, np.abs(v), np.abs(Bm), K, **kw)
+    return float(np.max(np.abs(got.astype(np.float64) - ref64) / np.maximum(scale, 1e-30)))
+
+
+# ----------------------------------------------------------------------------- CSR
+@pytest.mark.parametrize("K", [1, 7, 16, 32, 64, 100, 128, 256, 300, 516, 1030])
+def test_csrmm_rowmajor_widths(pkg, oracle, K):
+    rng = np.random.default_rng(K)
+    m, k = 777, 555
+    rp, ci, v = random_csr(rng, m, k, 9, hubs={5: 300, 700: 555}, empty_rows={0, 6, 776})
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C = torch.full((m, K), float("nan"), device="cuda")
+    pkg.gespmm_csrmm(m, K, dev(rp), dev(ci), dev(v), dev(B), C)
+    got = C.cpu().numpy()
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    assert err_vs(oracle, got, ref, rp, ci, v, B, K) <= TOL_FP32
+    # rows within one segment follow the reference kernel's FMA order exactly
+    seq = oracle.csrmm_f32_seq(rp, ci, v, B, K)
+    short = np.diff(rp) <= pkg.csrmm_segment(ci.size)
+    assert np.array_equal(got[short], seq[short])
+    assert np.all(got[[0, 6, 776]] == 0)  # empty rows are written (gespmm_csrmm.h:133-135)
+
+
+def test_csrmm_alpha_beta_and_ld(pkg, oracle):
+    rng = np.random.default_rng(3)
+    m, k, K, ldb, ldc = 300, 200, 64, 80, 72
+    rp, ci, v = random_csr(rng, m, k, 6, hubs={9: 150})
+    B = rng.uniform(-1, 1, (k, ldb)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, ldc)).astype(np.float32)
+    C = dev(C0)
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, k, K, ldb=ldb, ldc=ldc, alpha=0.5, beta=-2.0)
+    ref = oracle.csrmm(rp, ci, v, B, K, ldb=ldb, C0=C0, ldc=ldc, alpha=0.5, beta=-2.0)
+    got = C.cpu().numpy()
+    assert np.allclose(got[:, :K], ref, rtol=0, atol=2e-5)
+    assert np.array_equal(got[:, K:], C0[:, K:])  # padding columns untouched
+
+
+@pytest.mark.parametrize("b_layout,c_layout", [(1, 1), (0, 1), (1, 0)])
+def test_csrmm_cusparse_layouts(pkg, oracle, b_layout, c_layout):
+    # cusparseScsrmm (B, C column-major, run_csrmm.cu:135) and csrmm2+transB (B row-major, C column-major, :139)
+    rng = np.random.default_rng(11 + b_layout * 2 + c_layout)
+    m, k, K = 257, 131, 48
+    rp, ci, v = random_csr(rng, m, k, 5)
+    ldb = k + 3 if b_layout else K + 4
+    ldc = m + 5 if c_layout else K + 4
+    B = rng.uniform(-1, 1, (K if b_layout else k, ldb)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (K if c_layout else m, ldc)).astype(np.float32)
+    C = dev(C0)
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, k, K, ldb=ldb, b_layout=b_layout, ldc=ldc, c_layout=c_layout,
+              alpha=1.0, beta=1.0)
+    ref = oracle.csrmm(rp, ci, v, B, K, ldb=ldb, b_layout=b_layout, C0=C0, ldc=ldc, c_layout=c_layout, alpha=1.0,
+                       beta=1.0)
+    got = C.cpu().numpy()
+    got_mk = got[:, :m].T if c_layout else got[:, :K]
+    assert np.allclose(got_mk, ref, rtol=0, atol=2e-5)
+
+
+def test_csrmm_golden_g1_and_g4(pkg):
+    # csrmm.cu:47-99 (column-major B and C)
+    rp = np.array([0, 3, 4, 7, 9], np.int32)
+    ci = np.array([0, 2, 3, 1, 0, 2, 3, 1, 3], np.int32)
+    v = np.array([1, 2, 3, 4, 5, 6, 7, 8, 9], np.float32)
+    B = np.array([10, 20, 30, 40, 50, 60, 70, 80], np.float32)
+    C = torch.zeros(8, device="cuda")
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, 4, 4, 2, ldb=4, b_layout=1, ldc=4, c_layout=1)
+    assert C.cpu().tolist() == [190, 80, 510, 520, 430, 240, 1230, 1200]
+    # spmm.cc:45-52 (unit weights, row-major)
+    C = torch.zeros(2, 3, device="cuda")
+    pkg.gespmm_csrmm(2, 3, dev(np.array([0, 1, 3], np.int32)), dev(np.array([1, 0, 2], np.int32)),
+                     dev(np.ones(3, np.float32)), dev(np.array([[3, 9, 2], [4, 6, 7], [5, 8, 1]], np.float32)), C)
+    assert C.cpu().tolist() == [[4, 6, 7], [8, 17, 3]]
+
+
+def test_csrmm_long_rows_are_sharding_independent(pkg, oracle):
+    """Rows longer than a segment: deterministic, and identical whether the row is computed
+    inside the full matrix or inside a row shard (SURVEY 8e verification)."""
+    rng = np.random.default_rng(99)
+    m, k, K = 400, 3000, 128
+    rp, ci, v = random_csr(rng, m, k, 4, hubs={3: 2900, 150: 1000, 399: 65})
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    dB = dev(B)
+    full = torch.empty(m, K, device="cuda")
+    nnz = ci.size
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dB, full, m, k, K, nnz=nnz)
+    again = torch.empty(m, K, device="cuda")
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dB, again, m, k, K, nnz=nnz)
+    assert torch.equal(full, again)
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    assert err_vs(oracle, full.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32
+    # shard rows [100, 400): rebased rowptr, same segment length as the full matrix
+    lo = 100
+    rps = (rp[lo:] - rp[lo]).astype(np.int32)
+    cis, vs = ci[rp[lo]:], v[rp[lo]:]
+    part = torch.empty(m - lo, K, device="cuda")
+    pkg.csrmm(dev(rps), dev(cis), dev(vs), dB, part, m - lo, k, K, nnz=nnz)  # nnz of the WHOLE matrix fixes seg
+    assert torch.equal(part, full[lo:])
+
+
+def test_csrmm_empty_and_degenerate(pkg):
+    z = torch.zeros(1, dtype=torch.int32, device="cuda")
+    C = torch.zeros(0, 8, device="cuda")
+    pkg.csrmm(z, z[:0], torch.zeros(0, device="cuda"), torch.zeros(4, 8, device="cuda"), C, 0, 4, 8)
+    # all-empty rows
+    rp = torch.zeros(6, dtype=torch.int32, device="cuda")
+    C = torch.full((5, 8), 3.0, device="cuda")
+    pkg.csrmm(rp, z[:0], torch.zeros(0, device="cuda"), torch.ones(4, 8, device="cuda"), C, 5, 4, 8)
+    assert torch.all(C == 0)
+
+
+# ----------------------------------------------------------------------------- conversions
+@pytest.mark.parametrize("bs", [2, 3, 4, 8, 16, 32, 48, 64, 130])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_csr2bsr_bit_exact(pkg, oracle, bs, direction):
+    rng = np.random.default_rng(bs * 7 + direction)
+    m, n = 1000, 1200  # csr2bsr.cu:98-99 shape; ragged for most bs
+    rp, ci, v = random_csr(rng, m, n, 8, hubs={4: 900, 999: 1200}, empty_rows={0, 1, 2, 3} if bs == 4 else {10})
+    brp, bci, bv = pkg.csr2bsr(m, n, dev(rp), dev(ci), dev(v), bs, direction=direction)
+    orp, oci, ov = oracle.csr2bsr(rp, ci, v, m, n, bs, direction=direction)
+    assert np.array_equal(brp.cpu().numpy(), orp)
+    assert np.array_equal(bci.cpu().numpy(), oci)
+    assert np.array_equal(bv.cpu().numpy().view(np.uint32), ov.ravel().view(np.uint32))
+
+
+@pytest.mark.parametrize("bs", [2, 5, 16, 32, 64])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_bsr2csr_bit_exact(pkg, oracle, bs, direction):
+    rng = np.random.default_rng(bs + 100 * direction)
+    mb, nb = 150, 170
+    brp, bci, bv = random_bsr(rng, mb, nb, bs, 6, values="sparse")
+    crp, cci, cv = pkg.bsr2csr(mb, nb, dev(brp), dev(bci), dev(bv), bs, direction=direction)
+    orp, oci, ov = oracle.bsr2csr(brp, bci, bv, bs, direction=direction)
+    assert np.array_equal(crp.cpu().numpy(), orp)
+    assert np.array_equal(cci.cpu().numpy(), oci)
+    assert np.array_equal(cv.cpu().numpy().view(np.uint32), ov.view(np.uint32))
+
+
+def test_conversion_roundtrip_and_empty(pkg):
+    rng = np.random.default_rng(5)
+    m = n = 640
+    rp, ci, v = random_csr(rng, m, n, 7)
+    for bs in (4, 16, 32):
+        brp, bci, bv = pkg.csr2bsr(m, n, dev(rp), dev(ci), dev(v), bs)
+        crp, cci, cv = pkg.bsr2csr(m // bs, n // bs, brp, bci, bv, bs)
+        keep = cv != 0  # v has no exact zeros: dropping the fill recovers the input
+        assert torch.equal(cci[keep].cpu(), torch.from_numpy(ci))
+        assert torch.equal(cv[keep].cpu(), torch.from_numpy(v))
+    # empty matrix
+    rp0 = torch.zeros(m + 1, dtype=torch.int32, device="cuda")
+    brp, bci, bv = pkg.csr2bsr(m, n, rp0, rp0[:0], torch.zeros(0, device="cuda"), 16)
+    assert bci.numel() == 0 and torch.all(brp == 0)
+
+
+# ----------------------------------------------------------------------------- BSR
+def bsr_case(rng, mb, nb, bs, n, trans_b, c_layout, avg=5):
+    brp, bci, bv = random_bsr(rng, mb, nb, bs, avg)
+    k, m = nb * bs, mb * bs
+    ldb = (n + 4) if trans_b else (k + 8)
+    ldc = (m + 8) if c_layout == 1 else (n + 4)
+    B = rng.uniform(-1, 1, (k, ldb) if trans_b else (n, ldb)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (n, ldc) if c_layout == 1 else (m, ldc)).astype(np.float32)
+    return brp, bci, bv, B, C0, ldb, ldc
+
+
+def bsr_scale(oracle, brp, bci, bv, bs, B, n, ldb, trans_b, direction):
+    return oracle.bsrmm(brp, bci, np.abs(bv), bs, np.abs(B), n, ldb, trans_b, direction=direction)
+
+
+@pytest.mark.parametrize("bs", [2, 3, 4, 8, 16, 32, 40, 64])
+@pytest.mark.parametrize("trans_b", [0, 1])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_bsrmm_fp32(pkg, oracle, bs, trans_b, direction):
+    rng = np.random.default_rng(bs * 4 + trans_b * 2 + direction)
+    mb, nb, n = 37, 41, 70
+    brp, bci, bv, B, C0, ldb, ldc = bsr_case(rng, mb, nb, bs, n, trans_b, 1)
+    C = dev(C0)
+    rc = pkg.rocsparse_bsrmm(direction, 0, trans_b, mb, n, nb, bci.size, 0.75, dev(bv), dev(brp), dev(bci), bs,
+                             dev(B), ldb, -1.5, C, ldc)
+    assert rc == 0
+    ref = oracle.bsrmm(brp, bci, bv, bs, B, n, ldb, trans_b, direction=direction, alpha=0.75, beta=-1.5, C0=C0,
+                       ldc=ldc)
+    scale = 0.75 * bsr_scale(oracle, brp, bci, bv, bs, B, n, ldb, trans_b, direction) + 1.5 * np.abs(
+        C0[:, :mb * bs].T)
+    got = C.cpu().numpy()[:, :mb * bs].T
+    assert np.max(np.abs(got - ref) / np.maximum(scale, 1e-30)) <= TOL_FP32
+    assert np.array_equal(C.cpu().numpy()[:, mb * bs:], C0[:, mb * bs:])
+
+
+def test_bsrmm_golden_g2_g3(pkg):
+    # bsrmm.cu:50-61
+    C = torch.zeros(8, device="cuda")
+    pkg.bsrmm(0, 0, 2, 2, 3, 4, 1.0, dev(np.array([0, 4, 2, 7, 1, 8, 2, 0, 9, 0, 0, 2, 0, 6, 7, 0], np.float32)),
+              dev(np.array([0, 2, 4], np.int32)), dev(np.array([0, 2, 1, 2], np.int32)), 2,
+              dev(np.arange(1, 13, dtype=np.float32)), 6, 0.0, C, 4)
+    assert C.cpu().tolist() == [61, 26, 63, 43, 139, 92, 153, 97]
+    # block_cublas.cu:49-56,87-90
+    Z = torch.zeros(12, device="cuda")
+    pkg.block_gemm(2, 3, 3, 2, dev(np.array([0, 2, 3], np.int32)), dev(np.array([0, 1, 1], np.int32)),
+                   dev(np.array([0, 3, 1, 2, 4, 2, 0, 0, 0, 5, 0, 8], np.float32)),
+                   dev(np.array([6, 0, 0, 0, 7, 5, 4, 3, 0, 0, 0, 7], np.float32)), Z)
+    assert Z.cpu().tolist() == [16, 26, 0, 20, 19, 20, 0, 15, 5, 10, 0, 56]
+
+
+def test_bsrmm_status_codes(pkg):
+    z = torch.zeros(4, device="cuda")
+    zi = torch.zeros(4, dtype=torch.int32, device="cuda")
+    assert pkg.rocsparse_bsrmm(0, 1, 0, 1, 1, 1, 1, 1.0, z, zi, zi, 2, z, 2, 0.0, z, 2) == -2  # trans_A != N
+    assert pkg.rocsparse_bsrmm(0, 0, 0, 1, 1, 1, 1, 1.0, z, zi, zi, 2, z, 1, 0.0, z, 2) == -1  # ldb < kb*bs
+    assert pkg.rocsparse_bsrmm(0, 0, 0, 1, 1, 1, 0, 1.0, z, zi, zi, 2, z, 2, 0.0, z, 2) == 0   # nnzb == 0
+
+
+@pytest.mark.parametrize("math", [1, 2])
+@pytest.mark.parametrize("bs", [16, 32])
+@pytest.mark.parametrize("trans_b,c_layout", [(1, 0), (1, 1), (0, 1)])
+def test_bsrmm_tensor_core(pkg, oracle, math, bs, trans_b, c_layout):
+    rng = np.random.default_rng(bs + math * 3 + trans_b)
+    mb, nb, n = 67, 59, 128
+    brp, bci, bv = random_bsr(rng, mb, nb, bs, 9)
+    k, m = nb * bs, mb * bs
+    ldb = n if trans_b else k
+    ldc = m if c_layout == 1 else n
+    B = rng.uniform(-1, 1, (k, ldb) if trans_b else (n, ldb)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (n, ldc) if c_layout == 1 else (m, ldc)).astype(np.float32)
+    C = dev(C0)
+    pkg.bsrmm(0, trans_b, mb, n, nb, bci.size, 1.0, dev(bv), dev(brp), dev(bci), bs, dev(B), ldb, 1.0, C, ldc,
+              c_layout=c_layout, math=math)
+    ref = oracle.bsrmm(brp, bci, bv, bs, B, n, ldb, trans_b, alpha=1.0, beta=1.0, C0=C0, ldc=ldc, c_layout=c_layout)
+    scale = bsr_scale(oracle, brp, bci, bv, bs, B, n, ldb, trans_b, 0) + np.abs(C0.T if c_layout == 1 else C0)
+    got = C.cpu().numpy()
+    got = got.T if c_layout == 1 else got
+    assert np.max(np.abs(got - ref) / np.maximum(scale, 1e-30)) <= TOL_TC
+
+
+def test_check_result_harness(pkg, oracle):
+    """check_result.cu:99-261 through the new engine: csr2bsr(bs 4) + bsrmm(N,T) == csrmm2(N,T),
+    |z1 - z2| < 1e-4, on a Bernoulli(p) matrix with the +-0.5 checkerboard B."""
+    from spmm_denseblock_b200 import graphs
+    m = n = 4096
+    rp_t, ci_t = graphs.bernoulli_csr(m, n, 0.01, seed=1234)
+    rp, ci = rp_t.numpy(), ci_t.numpy()
+    rng = np.random.default_rng(1234)
+    v = rng.uniform(-1, 1, ci.size).astype(np.float32)
+    dim = 64
+    y = np.where(np.arange(n * dim) % 2 == 0, 0.5, -0.5).astype(np.float32)
+    z1 = torch.zeros(dim, m, device="cuda")  # column-major m x dim
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(y), z1, m, n, dim, ldb=dim, b_layout=0, ldc=m, c_layout=1)
+    brp, bci, bv = pkg.csr2bsr(m, n, dev(rp), dev(ci), dev(v), 4)
+    z2 = torch.zeros(dim, m, device="cuda")
+    pkg.bsrmm(0, 1, m // 4, dim, n // 4, bci.numel(), 1.0, bv, brp, bci, 4, dev(y), dim, 0.0, z2, m)
+    assert float((z1 - z2).abs().max()) < 1e-4
+    ref = oracle.csrmm(rp, ci, v, y, dim)
+    assert np.max(np.abs(z1.cpu().numpy().T - ref)) < 1e-4
