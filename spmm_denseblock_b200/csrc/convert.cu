@@ -270,7 +270,7 @@ extern "C" int spmmdb_csr2bsr_nnz(int m, int n, const int* rowptr, const int* co
     *nnzb_host = 0;
     return SPMMDB_OK;
   }
-  if (rowptr == nullptr || (colind == nullptr && m > 0)) return SPMMDB_ERR_INVALID_VALUE;
+  if (rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;  // colind may be null when nnz == 0
   const int ntiles = (mb + kScanTile - 1) / kScanTile;
   int* ws = (int*)scratch(kScratchConvert, sizeof(int) * ((size_t)mb + ntiles + 8), st);
   if (ws == nullptr) return SPMMDB_ERR_ALLOC;
@@ -296,9 +296,7 @@ extern "C" int spmmdb_csr2bsr_f32(int dir, int m, int n, const int* rowptr, cons
   if (device_sm() < 0) return SPMMDB_ERR_CUDA;
   const int mb = (m + block_dim - 1) / block_dim;
   if (mb == 0) return SPMMDB_OK;
-  if (rowptr == nullptr || colind == nullptr || val == nullptr || bsr_rowptr == nullptr || bsr_colind == nullptr ||
-      bsr_val == nullptr)
-    return SPMMDB_ERR_INVALID_VALUE;
+  if (rowptr == nullptr || bsr_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;  // others may be null when nnz == 0
   cudaStream_t st = (cudaStream_t)stream;
   if (block_dim <= 128)
     return launch_csr2bsr<1>(dir, m, mb, block_dim, rowptr, colind, val, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);

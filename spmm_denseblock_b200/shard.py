@@ -1,0 +1,24 @@
+"""nnz-balanced row sharding of a CSR matrix over the GPUs of one box (BASELINE.json
+north_star; the reference itself is single-GPU).  Output rows are disjoint, so the SpMM
+needs no reduction; B is replicated (all-gather of the row shards of B)."""
+import torch
+
+
+def nnz_balanced_ranges(rowptr, parts):
+    """Contiguous row ranges [lo_g, hi_g) holding ~nnz/parts non-zeros each:
+    boundary g = first row whose rowptr >= g*nnz/parts."""
+    n = rowptr.numel() - 1
+    nnz = int(rowptr[-1].item())
+    targets = torch.tensor([(g * nnz) // parts for g in range(1, parts)], dtype=rowptr.dtype, device=rowptr.device)
+    cuts = torch.searchsorted(rowptr, targets, right=False).clamp_(0, n).tolist() if parts > 1 else []
+    bounds = [0] + cuts + [n]
+    for i in range(1, len(bounds)):
+        bounds[i] = max(bounds[i], bounds[i - 1])
+    return [(bounds[g], bounds[g + 1]) for g in range(parts)]
+
+
+def shard_csr(rowptr, colind, val, lo, hi):
+    """Row slice [lo, hi) with rowptr rebased to 0; column ids stay global."""
+    s, e = int(rowptr[lo].item()), int(rowptr[hi].item())
+    rp = (rowptr[lo:hi + 1] - rowptr[lo]).contiguous()
+    return rp, colind[s:e].contiguous(), (val[s:e].contiguous() if val is not None else None)
