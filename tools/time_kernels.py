@@ -89,6 +89,9 @@ def main():
         elif case == "c2l":
             rp, ci = graphs.make_config_graph("c2_arxiv", device="cuda", scale=a.scale, p_local=0.8, window=512)
             csr_case("c2_arxiv_local", rp, ci, 128, flush)
+        elif case == "c4csr":
+            rp, ci = graphs.make_config_graph("c4_molhiv", device="cuda", scale=a.scale)
+            csr_case("c4_molhiv", rp, ci, 300, flush)
         elif case == "c4":
             rp, ci = graphs.make_config_graph("c4_molhiv", device="cuda", scale=a.scale)
             val, B, C = csr_case("c4_molhiv", rp, ci, 300, flush)
