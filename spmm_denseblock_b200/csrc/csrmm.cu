@@ -15,6 +15,8 @@
 // partial per segment and the group that finishes a row's last segment adds
 // the partials in segment order.  The split depends only on the row, so the
 // result is deterministic and independent of any row sharding.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace spmmdb {
@@ -42,6 +44,7 @@ struct CsrArgs {
   int cap_rows, cap_segs;
   int Kpad;             // K rounded up to 4
   int epoch;            // call counter: tells this call's queue entries from stale ones
+  int rpi;              // stream kernel: rows per work item (<= 32)
 };
 
 template <typename V> struct VecOps;
@@ -264,6 +267,184 @@ __global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
   }
 }
 
+
+// ---------------------------------------------------------------------------
+// Stream kernel (K % 4 == 0, K <= 512): persistent warps pull work items of
+// `rpi` consecutive rows from a global counter and walk the item's non-zero
+// stream [rowptr[r0], rowptr[r0 + rpi]) in coalesced chunks of 32 (col, val)
+// pairs, the next chunk prefetched while the current one is consumed.  B-row
+// gathers are issued U rows at a time ACROSS row boundaries, so short rows keep
+// the same memory-level parallelism as long ones; the FMA phase then walks the
+// batch in CSR order and stores a row whenever the stream crosses its end.  All
+// control flow is warp-uniform (every lane handles the same non-zero, VEC
+// float4 columns of it), and each output element is still the sequential fp32
+// FMA chain of the reference kernel.  Rows longer than `seg` are skipped here
+// and queued for csrmm_long_kernel.
+template <int VEC, int U, int MINB>
+__global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a) {
+  using Ops = VecOps<float4>;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int nvec = a.K >> 2;
+  const int nitems = (a.m + a.rpi - 1) / a.rpi;
+  const float4* __restrict__ Bv = reinterpret_cast<const float4*>(a.B) + lane;
+  const int64_t ldbv = a.ldb >> 2;
+  bool colok[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
+
+  int item = 0;
+  if (lane == 0) item = atomicAdd(a.counters + 3, 1);
+  item = __shfl_sync(FULL, item, 0);
+  while (item < nitems) {
+    int next_item = 0;
+    if (lane == 0) next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the loop
+
+    const int r0 = item * a.rpi;
+    const int nrows = min(a.rpi, a.m - r0);
+    int s = 0, e = 0;
+    if (lane < nrows) {
+      s = __ldg(a.rowptr + r0 + lane);
+      e = __ldg(a.rowptr + r0 + lane + 1);
+    }
+    int lng = (e - s) > a.seg;
+    if (__any_sync(FULL, lng)) {
+      if (lng) {
+        const int nseg = (e - s + a.seg - 1) / a.seg;
+        const int slot = atomicAdd(a.counters + 0, 1);
+        const int seg_base = atomicAdd(a.counters + 1, nseg);
+        if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
+          atomicExch(a.counters + 2, 1);
+          lng = 0;  // queue full (caller's nnz was too small): do the row here
+        } else {
+          a.long_rows[slot] = LongRow{r0 + lane, seg_base, nseg, a.epoch};
+          for (int t = 0; t < nseg; ++t) a.seg_owner[seg_base + t] = slot;
+        }
+      }
+    }
+    const int S = __shfl_sync(FULL, s, 0);
+    const int E = __shfl_sync(FULL, e, nrows - 1);
+
+    // current row state (warp-uniform)
+    int cr = 0;
+    int ce = __shfl_sync(FULL, e, 0);
+    int cl = __shfl_sync(FULL, lng, 0);
+    float4 acc[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+
+    auto flush_advance = [&]() {
+      if (!cl) {
+        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)(r0 + cr) * (a.ldc >> 2) + lane;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+          if (colok[i]) {
+            float4 out;
+            if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[32 * i]);
+            else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i]);
+            else out = acc[i];
+            __stcs(Cv + 32 * i, out);
+          }
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+      ++cr;
+      const int src = min(cr, 31);
+      ce = __shfl_sync(FULL, e, src);
+      cl = __shfl_sync(FULL, lng, src);
+      if (cr >= nrows) { ce = 0x7fffffff; cl = 1; }
+    };
+
+    int p0 = S & ~31;  // chunk base (128-byte aligned loads of colind / val)
+    int qn = S;        // next non-zero to consume
+    int c = 0;
+    float v = 0.f;
+    {
+      const int idx = p0 + lane;
+      if (idx >= S && idx < E) { c = __ldg(a.colind + idx); v = __ldg(a.val + idx); }
+    }
+    while (p0 < E) {
+      int c_n = 0;
+      float v_n = 0.f;
+      {
+        const int idx = p0 + 32 + lane;
+        if (idx < E) { c_n = __ldg(a.colind + idx); v_n = __ldg(a.val + idx); }
+      }
+      const int qhi = min(p0 + 32, E);
+#pragma unroll 1
+      for (int kk = (qn - p0) / U * U; p0 + kk < qhi; kk += U) {
+        float4 b[U][VEC];
+        float vv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int cc = __shfl_sync(FULL, c, kk + u);
+          vv[u] = __shfl_sync(FULL, v, kk + u);
+          const int q = p0 + kk + u;
+          if (q >= qn && q < qhi) {
+            const float4* __restrict__ brow = Bv + (int64_t)cc * ldbv;
+#pragma unroll
+            for (int i = 0; i < VEC; ++i)
+              if (colok[i]) b[u][i] = __ldg(brow + 32 * i);
+          }
+        }
+        const int q0 = p0 + kk;
+        if (q0 >= qn && q0 + U <= qhi && q0 + U <= ce && !cl) {
+          // whole batch inside the current row
+#pragma unroll
+          for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int i = 0; i < VEC; ++i)
+              if (colok[i]) Ops::fma(acc[i], vv[u], b[u][i]);
+        } else {
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int q = q0 + u;
+            if (q >= qn && q < qhi) {
+              while (q >= ce) flush_advance();
+              if (!cl) {
+#pragma unroll
+                for (int i = 0; i < VEC; ++i)
+                  if (colok[i]) Ops::fma(acc[i], vv[u], b[u][i]);
+              }
+            }
+          }
+        }
+      }
+      qn = qhi;
+      p0 += 32;
+      c = c_n;
+      v = v_n;
+      if (qn < E) {
+        while (qn >= ce) flush_advance();
+        if (cl) {
+          // inside a queued long row: jump to its end
+          qn = min(ce, E);
+          const int np0 = qn & ~31;
+          if (np0 != p0) {
+            p0 = np0;
+            const int idx = p0 + lane;
+            c = 0; v = 0.f;
+            if (idx >= qn && idx < E) { c = __ldg(a.colind + idx); v = __ldg(a.val + idx); }
+          }
+        }
+      }
+    }
+    while (cr < nrows) flush_advance();  // last row and trailing empty rows
+
+    item = __shfl_sync(FULL, next_item, 0);
+  }
+}
+
+template <int VEC, int U, int MINB>
+int launch_stream(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
+  csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  csrmm_long_kernel<float4, 32, VEC, (VEC >= 3 ? 4 : 8)><<<long_ctas, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
 template <typename V, int LPR, int VEC, int U>
 int launch_variant(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   constexpr int GPW = 32 / LPR;
@@ -316,11 +497,35 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.seg_owner = (int*)(q + hdr + sizeof(LongRow) * max_long);
   a.done = a.seg_owner + max_segs;
   a.partial = part;
-  SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 16, st));
-  const int nsm = device_num_sms();
-  const int long_ctas = (nsm > 0 ? nsm : 148) * 2;
+  SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  const int long_ctas = nsm * 2;
   const bool vec4 = (K % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
                     (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
+  static const int stream_min_k = [] { const char* e = getenv("SPMMDB_CSR_STREAM_MIN_K"); return e ? atoi(e) : 32; }();
+  if (vec4 && K >= stream_min_k && K <= 512) {
+    // rows per item: ~1024 non-zeros of work, at least ~4 items per resident warp
+    const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;
+    int rpi = 32;
+    while (rpi > 1 && rpi * avg > 1024) rpi >>= 1;
+    while (rpi > 1 && (int64_t)m / rpi < (int64_t)nsm * 32 * 4) rpi >>= 1;
+    a.rpi = rpi;
+    const int vec = (K / 4 + 31) / 32;
+    static const int variant = [] { const char* e = getenv("SPMMDB_CSR_VARIANT"); return e ? atoi(e) : 0; }();
+    if (vec == 1) {
+      if (variant == 1) return launch_stream<1, 16, 2>(a, nsm, long_ctas, st);
+      if (variant == 2) return launch_stream<1, 8, 3>(a, nsm, long_ctas, st);
+      return launch_stream<1, 8, 4>(a, nsm, long_ctas, st);
+    }
+    if (vec == 2) {
+      if (variant == 1) return launch_stream<2, 8, 2>(a, nsm, long_ctas, st);
+      if (variant == 2) return launch_stream<2, 4, 3>(a, nsm, long_ctas, st);
+      return launch_stream<2, 4, 4>(a, nsm, long_ctas, st);
+    }
+    if (vec == 3) return launch_stream<3, 3, 3>(a, nsm, long_ctas, st);
+    return launch_stream<4, 2, 3>(a, nsm, long_ctas, st);
+  }
+  a.rpi = 0;
   return vec4 ? dispatch<float4>(a, long_ctas, st) : dispatch<float>(a, long_ctas, st);
 }
 

@@ -1,0 +1,13 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests -m gpu -x -q -k "csrmm or check_result" > gpurun_out/pytest_csr.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_csr.log
+for v in 0 1 2; do
+  echo "== variant $v"
+  SPMMDB_CSR_VARIANT=$v timeout 600 python tools/time_kernels.py --cases c2,c2l,c4csr,c5,c5l,c3csr 2>&1 | python -c "
+import sys, json
+for l in sys.stdin:
+    try: d = json.loads(l)
+    except Exception: print(l.rstrip()); continue
+    print(d['case'], d['K'], 'ms_med %.4f ms_min %.4f gflops %.0f frac %.3f' % (d['ms_med'], d['ms_min'], d['gflops'], d['frac']))
+"
+done

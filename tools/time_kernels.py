@@ -103,6 +103,9 @@ def main():
         elif case == "c5l":
             rp, ci = graphs.make_config_graph("c5_products", device="cuda", scale=a.scale, p_local=0.9, window=4096)
             csr_case("c5_products_local", rp, ci, 256, flush)
+        elif case == "c3csr":
+            rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale)
+            csr_case("c3_proteins_ideal", rp, ci, 128, flush)
         elif case == "c3":
             rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale)
             val, B, C = csr_case("c3_proteins_ideal", rp, ci, 128, flush)
