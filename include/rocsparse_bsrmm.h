@@ -26,7 +26,7 @@
 
 #include "spmmdb.h"
 
-inline cusparseStatus_t spmmdb_to_cusparse_status(int rc) {
+inline cusparseStatus_t bsrmm_status_to_cusparse(int rc) {
   switch (rc) {
     case SPMMDB_OK: return CUSPARSE_STATUS_SUCCESS;
     case SPMMDB_ERR_INVALID_VALUE: return CUSPARSE_STATUS_INVALID_VALUE;
@@ -57,7 +57,7 @@ cusparseStatus_t rocsparse_bsrmm_template(cusparseHandle_t handle, cusparseDirec
                                   trans_B == CUSPARSE_OPERATION_TRANSPOSE ? 1 : 0, mb, n, kb, nnzb, block_dim, alpha,
                                   bsr_val, bsr_row_ptr, bsr_col_ind, B, ldb, beta, C, ldc, SPMMDB_COL_MAJOR,
                                   spmmdb_get_bsrmm_math(), stream);
-  return spmmdb_to_cusparse_status(rc);
+  return bsrmm_status_to_cusparse(rc);
 }
 
 #endif /* SPMMDB_DROPIN_ROCSPARSE_BSRMM_H */

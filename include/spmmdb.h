@@ -95,6 +95,12 @@ int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, 
                      const int* bsr_colind, const float* B, int64_t ldb, float beta, float* C,
                      int64_t ldc, int c_layout, int math, void* stream);
 
+/* Process-wide default arithmetic of the drop-in rocsparse_bsrmm_template<>
+ * (its signature has no `math` argument).  Initial value: the SPMMDB_BSRMM_MATH
+ * environment variable ("fp32" | "tf32" | "bf16"), else SPMMDB_MATH_FP32. */
+int spmmdb_set_bsrmm_math(int math);  /* SPMMDB_OK or SPMMDB_ERR_INVALID_VALUE */
+int spmmdb_get_bsrmm_math(void);
+
 /* --------------------------------------------------------------------------
  * Per-block GEMM formulation of BSR SpMM (block_cublas.cu:123-136,
  * test_block_cublas.cu:273-284): z(col-major, ld m) += A_blk(column-major

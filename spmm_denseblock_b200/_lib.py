@@ -28,6 +28,8 @@ SIGNATURES = {
     "spmmdb_csr2bsr_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp],
     "spmmdb_bsr2csr_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp],
     "spmmdb_csrmm_host_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, vp, C.c_float, C.c_float, vp],
+    "spmmdb_set_bsrmm_math": [C.c_int],
+    "spmmdb_get_bsrmm_math": [],
     "spmmdb_version": [],
     "spmmdb_last_error": [],
     "spmmdb_device_sm": [],

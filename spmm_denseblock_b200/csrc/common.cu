@@ -1,5 +1,6 @@
 // common.cu -- error capture, device queries and grow-only scratch for libspmmdb.
 #include <mutex>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -89,3 +90,24 @@ void* scratch(int slot, size_t bytes, cudaStream_t stream) {
 extern "C" const char* spmmdb_version(void) { return "spmmdb 0.1 (sm_100a)"; }
 extern "C" const char* spmmdb_last_error(void) { return spmmdb::g_last_error; }
 extern "C" int spmmdb_device_sm(void) { return spmmdb::device_sm(); }
+
+namespace {
+int g_bsrmm_math = -1;  // -1: not read from the environment yet
+int env_bsrmm_math() {
+  const char* e = getenv("SPMMDB_BSRMM_MATH");
+  if (e == nullptr) return SPMMDB_MATH_FP32;
+  if (strcmp(e, "tf32") == 0 || strcmp(e, "1") == 0) return SPMMDB_MATH_TF32;
+  if (strcmp(e, "bf16") == 0 || strcmp(e, "2") == 0) return SPMMDB_MATH_BF16;
+  return SPMMDB_MATH_FP32;
+}
+}  // namespace
+extern "C" int spmmdb_set_bsrmm_math(int math) {
+  if (math != SPMMDB_MATH_FP32 && math != SPMMDB_MATH_TF32 && math != SPMMDB_MATH_BF16)
+    return SPMMDB_ERR_INVALID_VALUE;
+  g_bsrmm_math = math;
+  return SPMMDB_OK;
+}
+extern "C" int spmmdb_get_bsrmm_math(void) {
+  if (g_bsrmm_math < 0) g_bsrmm_math = env_bsrmm_math();
+  return g_bsrmm_math;
+}
