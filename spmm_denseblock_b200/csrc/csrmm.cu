@@ -503,24 +503,29 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   const bool vec4 = (K % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
                     (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
   static const int stream_min_k = [] { const char* e = getenv("SPMMDB_CSR_STREAM_MIN_K"); return e ? atoi(e) : 32; }();
-  if (vec4 && K >= stream_min_k && K <= 512) {
-    // rows per item: ~1024 non-zeros of work, at least ~4 items per resident warp
+  // Long average rows (C3: 271 nnz/row) keep one warp per row: the rows kernel reaches the L2 gather
+  // ceiling there (0.94 ms vs 1.67 ms for the stream kernel, same profile file).
+  const bool dense_rows = m > 0 && nnz / m >= 64;
+  if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows) {
+    // rows per item: measured on B200 (profiles/r1b_csr_rpi_sweep.txt): 8 rows is the best or within 3% of it
+    // for avg degree 2 (C4), 6.5 (C2) and 24 (C5); fewer rows per item for denser rows.
     const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;
-    int rpi = 32;
-    while (rpi > 1 && rpi * avg > 1024) rpi >>= 1;
-    while (rpi > 1 && (int64_t)m / rpi < (int64_t)nsm * 32 * 4) rpi >>= 1;
+    int rpi = 8;
+    while (rpi > 1 && rpi * avg > 512) rpi >>= 1;
+    static const int rpi_env = [] { const char* e = getenv("SPMMDB_CSR_RPI"); return e ? atoi(e) : 0; }();
+    if (rpi_env > 0) rpi = rpi_env < 32 ? rpi_env : 32;
     a.rpi = rpi;
     const int vec = (K / 4 + 31) / 32;
     static const int variant = [] { const char* e = getenv("SPMMDB_CSR_VARIANT"); return e ? atoi(e) : 0; }();
     if (vec == 1) {
       if (variant == 1) return launch_stream<1, 16, 2>(a, nsm, long_ctas, st);
-      if (variant == 2) return launch_stream<1, 8, 3>(a, nsm, long_ctas, st);
-      return launch_stream<1, 8, 4>(a, nsm, long_ctas, st);
+      if (variant == 3) return launch_stream<1, 8, 4>(a, nsm, long_ctas, st);
+      return launch_stream<1, 8, 3>(a, nsm, long_ctas, st);
     }
     if (vec == 2) {
-      if (variant == 1) return launch_stream<2, 8, 2>(a, nsm, long_ctas, st);
       if (variant == 2) return launch_stream<2, 4, 3>(a, nsm, long_ctas, st);
-      return launch_stream<2, 4, 4>(a, nsm, long_ctas, st);
+      if (variant == 3) return launch_stream<2, 4, 4>(a, nsm, long_ctas, st);
+      return launch_stream<2, 8, 2>(a, nsm, long_ctas, st);
     }
     if (vec == 3) return launch_stream<3, 3, 3>(a, nsm, long_ctas, st);
     return launch_stream<4, 2, 3>(a, nsm, long_ctas, st);
