@@ -139,8 +139,10 @@ extern "C" int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int
   cudaStream_t st = (cudaStream_t)stream;
   if (math != SPMMDB_MATH_FP32 && bsrmm_tc_supported(trans_b, n, block_dim, ldb, B, bsr_val, c_layout, ldc, C)) {
     if (sm / 10 != 10) return SPMMDB_ERR_ARCH;
-    return bsrmm_tc(dir, trans_b, mb, n, kb, nnzb, block_dim, alpha, bsr_val, bsr_rowptr, bsr_colind, B, ldb, beta,
-                    C, ldc, c_layout, math, st);
+    const int rc = bsrmm_tc(dir, trans_b, mb, n, kb, nnzb, block_dim, alpha, bsr_val, bsr_rowptr, bsr_colind, B, ldb,
+                            beta, C, ldc, c_layout, math, st);
+    // a shape the tensor-core kernel does not lay out (tf32 with 64-wide blocks) runs the fp32 kernel
+    if (rc != SPMMDB_ERR_NOT_SUPPORTED) return rc;
   }
   return bsrmm_simt(dir, trans_b, mb, n, block_dim, alpha, bsr_val, bsr_rowptr, bsr_colind, B, ldb, beta, C, ldc,
                     c_layout, st);

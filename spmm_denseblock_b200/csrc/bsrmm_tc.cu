@@ -1,16 +1,629 @@
-// bsrmm_tc.cu -- BSR x dense on tcgen05 tensor cores (placeholder until the
-// kernel lands: reports "unsupported" so every call takes the fp32 kernel).
+// bsrmm_tc.cu -- BSR x dense on the sm_100a tensor cores (tcgen05.mma, kind::tf32 or
+// kind::f16 with bf16 inputs, fp32 accumulators in TMEM), operands staged by TMA.
+// Replaces bsrmm_large_blockdim_device / bsrmm_general_blockdim_device
+// (rocsparse_bsrmm_impl.h:315-472) and the per-block cublasSgemm loop of
+// block_cublas.cu:123-136 for block sizes 16 / 32 / 64.
+//
+// Formulation (transposed product, so that the gathered operand is the wide one):
+//   for a "super-row" of G = NT / bs consecutive block rows (NT rows of A) and every
+//   distinct column block j that occurs in it
+//       D[f, r] += sum_c  Bslab_j[c, f] * Astrip_j[r, c]        f < 128 features, r < NT, c < bs
+//   i.e. one tcgen05.mma with M = 128 (features), N = run * bs (a run of consecutive
+//   block rows that hold block j), K = bs.  The B slab (bs rows of B, all features) is
+//   fetched ONCE per super-row and column block and shared by all G block rows, which
+//   divides the L2 -> SM gather traffic of a plain per-block kernel by the number of
+//   blocks per strip.  D lives in TMEM: lane = feature, column = row of A.
+//
+//   operand "A" of the MMA = B slab:   row-major B[k][ldb] read by TMA boxes of
+//       {32 features, bs rows}, SWIZZLE_128B  -> MN-major (feature-major) canonical layout
+//   operand "B" of the MMA = A strip:  each bs x bs block is one TMA box {bs, bs} of
+//       bsr_val viewed as a [nnzb*bs][bs] matrix -> K-major (row-major blocks, DIR_ROW) or
+//       MN-major (column-major blocks, DIR_COLUMN) canonical layout, swizzle = row pitch
+//
+// Warp roles (192 threads, one persistent CTA per SM):
+//   warp 0      producer: pulls super-rows from a global counter, G-way merges the
+//               block rows' sorted column lists with warp votes, issues the TMA loads
+//   warp 1      MMA issuer (one elected lane): run detection, tcgen05.mma, tcgen05.commit
+//   warps 2..5  epilogue: tcgen05.ld of the finished accumulator, alpha/beta, stores to C
+// Two accumulator buffers in TMEM let the epilogue of super-row s overlap the MMAs of s+1.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace spmmdb {
+namespace {
 
-bool bsrmm_tc_supported(int, int, int, int64_t, const float*, const float*, int, int64_t, const float*) {
-  return false;
+constexpr int kThreads = 192;
+constexpr int kMaxStages = 8;
+constexpr uint32_t kEndFlag = 0x80000000u;  // step meta: end of a super-row
+
+// ---------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
 
-int bsrmm_tc(int, int, int, int, int, int64_t, int, float, const float*, const int*, const int*, const float*,
-             int64_t, float, float*, int64_t, int, int, cudaStream_t) {
-  return SPMMDB_ERR_NOT_SUPPORTED;
+__device__ __forceinline__ void tmem_alloc_512(uint32_t* slot) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(slot)) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_512(uint32_t addr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+template <bool BF16>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (BF16) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// 32 lanes x 32 consecutive columns -> 32 registers per thread (thread = TMEM lane)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address,
+// leading / stride byte offsets in 16-byte units, version 1 (Blackwell), swizzle mode.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr >> 4) & 0x3fffu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+constexpr uint32_t kLayoutSw128 = 2, kLayoutSw64 = 4, kLayoutSw32 = 6, kLayoutSw128B32 = 1;
+
+struct TcArgs {
+  int mb, n, bs, G, NT, tiles, nchunks, stages;
+  int dir, c_layout;
+  int num_super;
+  const int* rowptr;
+  const int* colind;
+  float* C;
+  int64_t ldc;
+  float alpha, beta;
+  int* counter;
+  uint32_t chunk_bytes;   // bs * 128: one {128-byte feature chunk, bs rows} TMA box of B
+  uint32_t block_bytes;   // bs * bs * esize: one block of A
+  uint32_t stage_b_bytes; // tiles * chunks_per_tile * chunk_bytes
+  uint32_t stage_bytes;   // stage_b_bytes + NT * bs * esize, multiple of 1024
+};
+
+struct StepMeta { uint32_t mask; int s; };
+struct AccInfo { int s; uint32_t touched; };
+
+struct __align__(8) TcSmemCtl {
+  uint64_t full[kMaxStages];
+  uint64_t empty[kMaxStages];
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  StepMeta meta[kMaxStages];
+  AccInfo acc[2];
+  uint32_t tmem_base;
+};
+
+template <bool BF16>
+__global__ void __launch_bounds__(kThreads, 1)
+bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapA) {
+  constexpr int ESIZE = BF16 ? 2 : 4;
+  constexpr int FC = 128 / ESIZE;           // features per 128-byte chunk
+  constexpr int CPT = 128 / FC;             // chunks per 128-feature tile
+  constexpr int KI = 32 / ESIZE;            // K of one tcgen05.mma
+  constexpr uint32_t FMT = BF16 ? 1u : 2u;  // F16F32Format: BF16 = 1, TF32 = 2
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // stage buffers first (1024-byte aligned for the 128B swizzle), control block after them
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  TcSmemCtl* ctl = (TcSmemCtl*)(smem + (size_t)a.stages * a.stage_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < a.stages; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&ctl->tmem_full[i], 2); mbar_init(&ctl->tmem_empty[i], 4); }
+    fence_barrier_init();
+    tma_prefetch_desc(&mapB);
+    tma_prefetch_desc(&mapA);
+  }
+  if (warp == 2) tmem_alloc_512(&ctl->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = ctl->tmem_base;
+  const int acc_cols = a.tiles * a.NT;  // <= 256
+
+  if (warp == 0) {
+    // ===================== producer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    constexpr int W = 8;  // column-index look-ahead window per block row
+    while (true) {
+      int s = 0;
+      if (lane == 0) s = atomicAdd(a.counter, 1);
+      s = __shfl_sync(0xffffffffu, s, 0);
+      if (s >= a.num_super) {
+        mbar_wait(&ctl->empty[stage], phase ^ 1);
+        if (lane == 0) {
+          ctl->meta[stage].mask = kEndFlag;
+          ctl->meta[stage].s = -1;
+          mbar_arrive(&ctl->full[stage]);
+        }
+        break;
+      }
+      const int br = s * a.G + lane;
+      int cur = 0, end = 0;
+      if (lane < a.G && br < a.mb) { cur = __ldg(a.rowptr + br); end = __ldg(a.rowptr + br + 1); }
+      int q[W];
+      int have = 0;  // valid look-ahead entries (same for every lane by construction)
+      while (true) {
+        if (have == 0) {
+#pragma unroll
+          for (int i = 0; i < W; ++i) q[i] = (cur + i < end) ? __ldg(a.colind + cur + i) : 0x7fffffff;
+          have = W;
+        }
+        const int col = q[0];
+        int jmin = col;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) jmin = min(jmin, __shfl_xor_sync(0xffffffffu, jmin, o));
+        if (jmin == 0x7fffffff) break;
+        const bool mine = (col == jmin);
+        const uint32_t present = __ballot_sync(0xffffffffu, mine);
+        mbar_wait(&ctl->empty[stage], phase ^ 1);
+        uint8_t* sB = smem + (size_t)stage * a.stage_bytes;
+        uint8_t* sA = sB + a.stage_b_bytes;
+        if (lane == 0) {
+          ctl->meta[stage].mask = present;
+          mbar_arrive_expect_tx(&ctl->full[stage], a.nchunks * a.chunk_bytes + __popc(present) * a.block_bytes);
+        }
+        __syncwarp();
+        if (lane < a.nchunks) tma_load_2d(sB + (size_t)lane * a.chunk_bytes, &mapB, lane * FC, jmin * a.bs, &ctl->full[stage]);
+        if (mine) {
+          tma_load_2d(sA + (size_t)lane * a.block_bytes, &mapA, 0, cur * a.bs, &ctl->full[stage]);
+          ++cur;
+#pragma unroll
+          for (int i = 0; i + 1 < W; ++i) q[i] = q[i + 1];
+          q[W - 1] = 0x7fffffff;
+        }
+        // a lane that advanced W times has an empty window: refill everybody together
+        const bool dry = mine && (cur < end) && (q[0] == 0x7fffffff);
+        have = __any_sync(0xffffffffu, dry) ? 0 : have;
+        if (++stage == a.stages) { stage = 0; phase ^= 1; }
+      }
+      // end of the super-row
+      mbar_wait(&ctl->empty[stage], phase ^ 1);
+      if (lane == 0) {
+        ctl->meta[stage].mask = kEndFlag;
+        ctl->meta[stage].s = s;
+        mbar_arrive(&ctl->full[stage]);
+      }
+      if (++stage == a.stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase[2] = {0, 0};
+      const uint32_t rp = (uint32_t)a.bs * ESIZE;  // row pitch of a block in shared memory
+      const uint32_t a_layout = rp == 128 ? kLayoutSw128 : (rp == 64 ? kLayoutSw64 : kLayoutSw32);
+      const uint32_t idesc_base = (1u << 4) | (FMT << 7) | (FMT << 10) | (1u << 15) |
+                                  ((a.dir == SPMMDB_DIR_COLUMN ? 1u : 0u) << 16) | ((128u >> 4) << 24);
+      const int ksteps = a.bs / KI;
+      bool done = false;
+      while (!done) {
+        mbar_wait(&ctl->tmem_empty[acc], acc_phase[acc] ^ 1);
+        tc_fence_after();
+        uint32_t touched = 0;
+        while (true) {
+          mbar_wait(&ctl->full[stage], phase);
+          tc_fence_after();
+          const uint32_t mask = ctl->meta[stage].mask;
+          if (mask & kEndFlag) {
+            const int s = ctl->meta[stage].s;
+            ctl->acc[acc].s = s;
+            ctl->acc[acc].touched = touched;
+            mbar_arrive(&ctl->tmem_full[acc]);  // release: publishes acc[] to the epilogue
+            umma_commit(&ctl->tmem_full[acc]);  // arrives when every MMA issued so far has completed
+            mbar_arrive(&ctl->empty[stage]);
+            if (++stage == a.stages) { stage = 0; phase ^= 1; }
+            if (s < 0) done = true;
+            break;
+          }
+          const uint32_t sB = smem_u32(smem + (size_t)stage * a.stage_bytes);
+          const uint32_t sA = sB + a.stage_b_bytes;
+          for (int t = 0; t < a.tiles; ++t) {
+            uint32_t m = mask;
+            while (m) {
+              const int l0 = __ffs(m) - 1;
+              const uint32_t tb = (touched >> l0) & 1u;
+              int len = 1;
+              while (l0 + len < a.G && ((m >> (l0 + len)) & 1u) && ((touched >> (l0 + len)) & 1u) == tb &&
+                     (len + 1) * a.bs <= 256)
+                ++len;
+              m &= ~(((1u << len) - 1u) << l0);
+              const uint32_t idesc = idesc_base | ((uint32_t)(len * a.bs) >> 3) << 17;
+              const uint32_t d = tmem_base + (uint32_t)(acc * acc_cols + t * a.NT + l0 * a.bs);
+              for (int ks = 0; ks < ksteps; ++ks) {
+                // MMA operand A = B slab, MN-major SW128: 8 k-rows x 128 B per core group,
+                // feature chunks LBO apart, k groups SBO = 1024 B apart
+                // (tf32: MN-major 32-bit operands exist only in the 128B-swizzle-with-32B-atoms layout,
+                //  whose k groups are 4 rows = 512 B)
+                const uint64_t adesc = smem_desc(sB + (uint32_t)(t * CPT) * a.chunk_bytes + (uint32_t)ks * KI * 128u,
+                                                 a.chunk_bytes, BF16 ? 1024u : 512u, BF16 ? kLayoutSw128 : kLayoutSw128B32);
+                uint64_t bdesc;
+                if (a.dir == SPMMDB_DIR_ROW)  // K-major: advance inside the swizzle atom by 32 B per k-step
+                  bdesc = smem_desc(sA + (uint32_t)l0 * a.block_bytes + (uint32_t)ks * 32u, 16u, 8u * rp, a_layout);
+                else  // MN-major: blocks (n chunks) LBO apart, k groups of 8 rows SBO apart
+                  bdesc = smem_desc(sA + (uint32_t)l0 * a.block_bytes + (uint32_t)ks * KI * rp, a.block_bytes, 8u * rp,
+                                    a_layout);
+                umma<BF16>(d, adesc, bdesc, idesc, (tb | (ks > 0)) ? 1u : 0u);
+              }
+            }
+          }
+          touched |= mask;
+          umma_commit(&ctl->empty[stage]);  // frees the stage when these MMAs have read it
+          if (++stage == a.stages) { stage = 0; phase ^= 1; }
+        }
+        acc_phase[acc] ^= 1;
+        acc ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+    const int qd = warp & 3;  // TMEM lane quarter this warp may access
+    int acc = 0;
+    uint32_t full_phase[2] = {0, 0};
+    const int64_t m_rows = (int64_t)a.mb * a.bs;
+    while (true) {
+      mbar_wait(&ctl->tmem_full[acc], full_phase[acc]);
+      tc_fence_after();
+      const int s = ctl->acc[acc].s;
+      const uint32_t touched = ctl->acc[acc].touched;
+      if (s < 0) break;
+      for (int t = 0; t < a.tiles; ++t) {
+        const int f = t * 128 + qd * 32 + lane;
+        const bool fok = f < a.n;
+        for (int c0 = 0; c0 < a.NT; c0 += 32) {
+          const int64_t row0 = (int64_t)s * a.NT + c0;
+          if (row0 >= m_rows) break;
+          uint32_t v[32];
+          // block rows covered by these 32 columns
+          const int lb = c0 / a.bs, le = (c0 + 31) / a.bs;
+          uint32_t any = 0;
+          for (int l = lb; l <= le; ++l) any |= (touched >> l) & 1u;
+          if (any) {
+            tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(acc * acc_cols + t * a.NT + c0), v);
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int l = (c0 + j) / a.bs;
+            if (!any || !((touched >> l) & 1u)) v[j] = 0u;
+          }
+          if (!fok) continue;
+          if (a.c_layout == SPMMDB_ROW_MAJOR) {
+            float* __restrict__ cp = a.C + row0 * a.ldc + f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (row0 + j < m_rows) {
+                float o = a.alpha * __uint_as_float(v[j]);
+                if (a.beta != 0.f) o = fmaf(a.beta, cp[(int64_t)j * a.ldc], o);
+                cp[(int64_t)j * a.ldc] = o;
+              }
+            }
+          } else {
+            float* __restrict__ cp = a.C + (int64_t)f * a.ldc + row0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (row0 + j < m_rows) {
+                float o = a.alpha * __uint_as_float(v[j]);
+                if (a.beta != 0.f) o = fmaf(a.beta, cp[j], o);
+                cp[j] = o;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->tmem_empty[acc]);
+      full_phase[acc] ^= 1;
+      acc ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc_512(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------
+// Pre-passes (only when the caller's operands cannot be read by TMA as they are)
+// ---------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ T cvt_out(float v);
+template <> __device__ __forceinline__ float cvt_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// out[r * ldo + c] = B(r, c) for r < rows, c < cols; B row-major (ldb >= cols) or column-major (ldb >= rows)
+template <typename T>
+__global__ void __launch_bounds__(256) prep_b_kernel(const float* __restrict__ B, int64_t ldb, int col_major, T* out,
+                                                     int64_t ldo, int rows, int cols) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+  if (col_major) {
+    for (int i = ty; i < 32; i += 8) {
+      const int64_t c = c0 + i, r = r0 + tx;
+      tile[i][tx] = (c < cols && r < rows) ? B[c * ldb + r] : 0.f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+      const int64_t r = r0 + i, c = c0 + tx;
+      if (r < rows && c < cols) out[r * ldo + c] = cvt_out<T>(tile[tx][i]);
+    }
+  } else {
+    for (int i = ty; i < 32; i += 8) {
+      const int64_t r = r0 + i, c = c0 + tx;
+      if (r < rows && c < cols) out[r * ldo + c] = cvt_out<T>(B[r * ldb + c]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) cvt_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, int64_t n4) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = __ldcs(in + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    out[i] = o;
+  }
+}
+
+// out block [r][c] = in block [c][r]: column-major blocks -> row-major blocks (tf32 path only: 32-bit
+// MN-major operands need 128-byte rows, which a 16-wide block does not have)
+__global__ void __launch_bounds__(256) block_transpose_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                              int bs, int64_t nnzb) {
+  const int64_t bs2 = (int64_t)bs * bs;
+  const int64_t total = nnzb * bs2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t p = i / bs2;
+    const int e = (int)(i - p * bs2);
+    const int r = e / bs, c = e - r * bs;
+    out[i] = __ldg(in + p * bs2 + (int64_t)c * bs + r);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+bool make_map_2d(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer, uint64_t row_bytes,
+                 uint32_t box_inner, uint32_t box_outer, uint32_t swizzle_bytes) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapSwizzle sw = swizzle_bytes == 129 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                          : swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                          : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUresult r = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+}  // namespace
+
+// Shapes the tensor-core kernel takes; everything else runs the fp32 CUDA-core kernel.
+bool bsrmm_tc_supported(int trans_b, int n, int bs, int64_t ldb, const float* B, const float* val, int c_layout,
+                        int64_t ldc, const float* C) {
+  (void)trans_b; (void)ldb; (void)B; (void)c_layout; (void)ldc; (void)C;
+  if (bs != 16 && bs != 32 && bs != 64) return false;
+  if (n < 1) return false;
+  if (((uintptr_t)val) % 16 != 0) return false;
+  return encode_fn() != nullptr;
+}
+
+int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, float alpha, const float* val,
+             const int* rowptr, const int* colind, const float* B, int64_t ldb, float beta, float* C, int64_t ldc,
+             int c_layout, int math, cudaStream_t st) {
+  // n > 512 features: column slabs of 512 (TMEM holds 512 accumulator columns)
+  if (n > 512) {
+    for (int c0 = 0; c0 < n; c0 += 512) {
+      const int nn = n - c0 < 512 ? n - c0 : 512;
+      const float* Bs = trans_b ? B + c0 : B + (int64_t)c0 * ldb;
+      float* Cs = c_layout == SPMMDB_ROW_MAJOR ? C + c0 : C + (int64_t)c0 * ldc;
+      int rc = bsrmm_tc(dir, trans_b, mb, nn, kb, nnzb, bs, alpha, val, rowptr, colind, Bs, ldb, beta, Cs, ldc,
+                        c_layout, math, st);
+      if (rc != SPMMDB_OK) return rc;
+    }
+    return SPMMDB_OK;
+  }
+  bool bf16 = (math == SPMMDB_MATH_BF16);
+  if (!bf16 && bs == 64) bf16 = false;  // tf32 with 256-byte block rows: see below
+  const int esize = bf16 ? 2 : 4;
+  if (bs * esize > 128) {
+    // a block row wider than the 128-byte swizzle span (tf32, bs = 64) is not laid out by one TMA box
+    return SPMMDB_ERR_NOT_SUPPORTED;
+  }
+  const int64_t krows = (int64_t)kb * bs;
+  const int fc = 128 / esize;
+  const int tiles = (n + 127) / 128;
+  const int nchunks = (n + fc - 1) / fc;
+
+  // ---- operand B: TMA needs row-major [krows][ld] with a 16-byte aligned base and row pitch ----
+  const void* Bt = B;
+  int64_t ldbt = ldb;
+  const bool b_direct = !bf16 && trans_b == 1 && (ldb % 4 == 0) && ((uintptr_t)B % 16 == 0);
+  if (!b_direct) {
+    const int64_t ldo = ((int64_t)n + 7) & ~(int64_t)7;
+    void* sb = scratch(kScratchBsrB, (size_t)krows * ldo * esize, st);
+    if (sb == nullptr) return SPMMDB_ERR_ALLOC;
+    dim3 grid((unsigned)((krows + 31) / 32), (unsigned)((n + 31) / 32));
+    if (bf16)
+      prep_b_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(B, ldb, trans_b == 0, (__nv_bfloat16*)sb, ldo, (int)krows, n);
+    else
+      prep_b_kernel<float><<<grid, 256, 0, st>>>(B, ldb, trans_b == 0, (float*)sb, ldo, (int)krows, n);
+    SPMMDB_CUDA_OK(cudaGetLastError());
+    Bt = sb;
+    ldbt = ldo;
+  }
+  // ---- operand A: fp32 blocks are read as tf32 in place; bf16 needs a converted copy ----
+  const void* At = val;
+  if (bf16) {
+    const int64_t elems = nnzb * bs * bs;
+    void* sa = scratch(kScratchBsrA, (size_t)elems * 2, st);
+    if (sa == nullptr) return SPMMDB_ERR_ALLOC;
+    const int64_t n4 = elems / 4;  // bs*bs is a multiple of 4
+    int blocks = (int)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
+    cvt_bf16_kernel<<<blocks, 256, 0, st>>>((const float4*)val, (uint2*)sa, n4);
+    SPMMDB_CUDA_OK(cudaGetLastError());
+    At = sa;
+  }
+
+  if (!bf16 && dir == SPMMDB_DIR_COLUMN) {
+    const int64_t elems = nnzb * bs * bs;
+    void* sa = scratch(kScratchBsrA, (size_t)elems * 4, st);
+    if (sa == nullptr) return SPMMDB_ERR_ALLOC;
+    int blocks = (int)((elems + 255) / 256 < 148 * 16 ? (elems + 255) / 256 : 148 * 16);
+    block_transpose_kernel<<<blocks, 256, 0, st>>>(val, (float*)sa, bs, nnzb);
+    SPMMDB_CUDA_OK(cudaGetLastError());
+    At = sa;
+    dir = SPMMDB_DIR_ROW;
+  }
+
+  TcArgs a;
+  a.mb = mb; a.n = n; a.bs = bs; a.tiles = tiles; a.nchunks = nchunks;
+  static const int nt_env = [] { const char* e = getenv("SPMMDB_BSR_NT"); return e ? atoi(e) : 0; }();
+  int NT = tiles <= 2 ? 128 : 64;
+  if (nt_env == 64 || nt_env == 128 || nt_env == 256) NT = nt_env;
+  while (NT * tiles > 256) NT >>= 1;
+  if (NT < bs) return SPMMDB_ERR_NOT_SUPPORTED;  // bs = 64 with > 4 tiles cannot happen (n <= 512)
+  a.NT = NT;
+  a.G = NT / bs;
+  a.dir = dir; a.c_layout = c_layout;
+  a.num_super = (mb + a.G - 1) / a.G;
+  a.rowptr = rowptr; a.colind = colind; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
+  a.chunk_bytes = (uint32_t)bs * 128u;
+  a.block_bytes = (uint32_t)(bs * bs * esize);
+  const int cpt = 128 / fc;
+  a.stage_b_bytes = (uint32_t)(tiles * cpt) * a.chunk_bytes;
+  a.stage_bytes = (a.stage_b_bytes + (uint32_t)(NT * bs * esize) + 1023u) & ~1023u;
+  const size_t ctl_bytes = sizeof(TcSmemCtl) + 64;
+  const size_t smem_max = 227 * 1024;
+  int stages = (int)((smem_max - 1024 - ctl_bytes) / a.stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return SPMMDB_ERR_NOT_SUPPORTED;
+  a.stages = stages;
+  const size_t smem_bytes = 1024 + (size_t)stages * a.stage_bytes + ctl_bytes;
+
+  int* counter = (int*)scratch(kScratchBsr, 256, st);
+  if (counter == nullptr) return SPMMDB_ERR_ALLOC;
+  SPMMDB_CUDA_OK(cudaMemsetAsync(counter, 0, 4, st));
+  a.counter = counter;
+
+  CUtensorMap mapB, mapA;
+  if (!make_map_2d(&mapB, bf16, Bt, (uint64_t)n, (uint64_t)krows, (uint64_t)ldbt * esize, (uint32_t)fc, (uint32_t)bs, bf16 ? 128 : 129))
+    return SPMMDB_ERR_INVALID_VALUE;
+  if (!make_map_2d(&mapA, bf16, At, (uint64_t)bs, (uint64_t)nnzb * bs, (uint64_t)bs * esize, (uint32_t)bs, (uint32_t)bs,
+                   (uint32_t)(bs * esize)))
+    return SPMMDB_ERR_INVALID_VALUE;
+
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  const int grid = a.num_super < nsm ? a.num_super : nsm;
+  if (bf16) {
+    SPMMDB_CUDA_OK(cudaFuncSetAttribute(bsrmm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    bsrmm_tc_kernel<true><<<grid, kThreads, smem_bytes, st>>>(a, mapB, mapA);
+  } else {
+    SPMMDB_CUDA_OK(cudaFuncSetAttribute(bsrmm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    bsrmm_tc_kernel<false><<<grid, kThreads, smem_bytes, st>>>(a, mapB, mapA);
+  }
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
 }
 
 }  // namespace spmmdb

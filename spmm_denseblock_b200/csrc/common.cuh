@@ -25,7 +25,7 @@ void set_last_error(const char* what, cudaError_t err, const char* file, int lin
 // (cudaMalloc synchronises, steady-state calls stay asynchronous).  Newly
 // allocated memory is zero-filled.
 enum ScratchSlot { kScratchCsrLong = 0, kScratchCsrPartial, kScratchLayoutB, kScratchLayoutC,
-                   kScratchConvert, kScratchBsr, kScratchHostA, kScratchHostB, kScratchHostC,
+                   kScratchConvert, kScratchBsr, kScratchBsrA, kScratchBsrB, kScratchHostA, kScratchHostB, kScratchHostC,
                    kScratchSlots };
 void* scratch(int slot, size_t bytes, cudaStream_t stream);
 

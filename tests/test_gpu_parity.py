@@ -242,25 +242,73 @@ def test_bsrmm_status_codes(pkg):
 
 
 @pytest.mark.parametrize("math", [1, 2])
-@pytest.mark.parametrize("bs", [16, 32])
-@pytest.mark.parametrize("trans_b,c_layout", [(1, 0), (1, 1), (0, 1)])
-def test_bsrmm_tensor_core(pkg, oracle, math, bs, trans_b, c_layout):
-    rng = np.random.default_rng(bs + math * 3 + trans_b)
-    mb, nb, n = 67, 59, 128
+@pytest.mark.parametrize("bs", [16, 32, 64])
+@pytest.mark.parametrize("direction", [0, 1])
+@pytest.mark.parametrize("trans_b,c_layout,n", [(1, 0, 128), (1, 1, 128), (0, 1, 128), (1, 0, 300), (0, 1, 44)])
+def test_bsrmm_tensor_core(pkg, oracle, math, bs, direction, trans_b, c_layout, n):
+    """tcgen05 path (tf32 / bf16 inputs, fp32 accumulate): relative error <= 1e-2 (north_star),
+    alpha/beta applied, every layout the reference interface has, ragged feature counts."""
+    rng = np.random.default_rng(bs + math * 3 + trans_b + 7 * direction + n)
+    mb, nb = 67, 59
     brp, bci, bv = random_bsr(rng, mb, nb, bs, 9)
+    brp, bci, bv = _drop_row(brp, bci, bv, 4, bs)
     k, m = nb * bs, mb * bs
     ldb = n if trans_b else k
     ldc = m if c_layout == 1 else n
     B = rng.uniform(-1, 1, (k, ldb) if trans_b else (n, ldb)).astype(np.float32)
     C0 = rng.uniform(-1, 1, (n, ldc) if c_layout == 1 else (m, ldc)).astype(np.float32)
     C = dev(C0)
-    pkg.bsrmm(0, trans_b, mb, n, nb, bci.size, 1.0, dev(bv), dev(brp), dev(bci), bs, dev(B), ldb, 1.0, C, ldc,
+    pkg.bsrmm(direction, trans_b, mb, n, nb, bci.size, 0.5, dev(bv), dev(brp), dev(bci), bs, dev(B), ldb, 2.0, C, ldc,
               c_layout=c_layout, math=math)
-    ref = oracle.bsrmm(brp, bci, bv, bs, B, n, ldb, trans_b, alpha=1.0, beta=1.0, C0=C0, ldc=ldc, c_layout=c_layout)
-    scale = bsr_scale(oracle, brp, bci, bv, bs, B, n, ldb, trans_b, 0) + np.abs(C0.T if c_layout == 1 else C0)
+    ref = oracle.bsrmm(brp, bci, bv, bs, B, n, ldb, trans_b, direction=direction, alpha=0.5, beta=2.0, C0=C0, ldc=ldc,
+                       c_layout=c_layout)
+    scale = 0.5 * bsr_scale(oracle, brp, bci, bv, bs, B, n, ldb, trans_b, direction) + 2.0 * np.abs(
+        C0.T if c_layout == 1 else C0)
     got = C.cpu().numpy()
     got = got.T if c_layout == 1 else got
-    assert np.max(np.abs(got - ref) / np.maximum(scale, 1e-30)) <= TOL_TC
+    err = np.max(np.abs(got - ref) / np.maximum(scale, 1e-30))
+    assert err <= TOL_TC, err
+    # the tensor-core path must really have run: bf16 rounding is visible, fp32 would be ~1e-7
+    if math == 2:
+        assert err > 1e-5
+
+
+def _drop_row(brp, bci, bv, row, bs):
+    """Remove every block of block row `row` (an empty block row in the middle of a super-row)."""
+    lo, hi = int(brp[row]), int(brp[row + 1])
+    cnt = hi - lo
+    bci = np.concatenate([bci[:lo], bci[hi:]])
+    bv = np.concatenate([bv[:lo * bs * bs], bv[hi * bs * bs:]])
+    brp = brp.copy()
+    brp[row + 1:] -= cnt
+    return brp, bci.astype(np.int32), bv.astype(np.float32)
+
+
+def test_bsrmm_tensor_core_dense_strip_and_empty(pkg, oracle):
+    """Super-rows whose block rows share every column block (one wide MMA per step), a fully empty
+    super-row, and a ragged last super-row (mb not a multiple of the group size)."""
+    rng = np.random.default_rng(77)
+    bs, mb, nb, n = 16, 21, 12, 128
+    rows = []
+    for i in range(mb):
+        if 8 <= i < 16:
+            rows.append(np.zeros(0, np.int64))  # super-row 1 (block rows 8..15) is empty
+        else:
+            rows.append(np.arange(nb))           # dense strips
+    brp = np.zeros(mb + 1, np.int32)
+    brp[1:] = np.cumsum([len(r) for r in rows])
+    bci = np.concatenate(rows).astype(np.int32)
+    bv = rng.uniform(-1, 1, bci.size * bs * bs).astype(np.float32)
+    B = rng.uniform(-1, 1, (nb * bs, n)).astype(np.float32)
+    for math in (1, 2):
+        C = torch.full((mb * bs, n), float("nan"), device="cuda")
+        pkg.bsrmm(0, 1, mb, n, nb, bci.size, 1.0, dev(bv), dev(brp), dev(bci), bs, dev(B), n, 0.0, C, n, c_layout=0,
+                  math=math)
+        ref = oracle.bsrmm(brp, bci, bv, bs, B, n, n, 1)
+        scale = bsr_scale(oracle, brp, bci, bv, bs, B, n, n, 1, 0)
+        got = C.cpu().numpy()
+        assert np.all(got[8 * bs:16 * bs] == 0)
+        assert np.max(np.abs(got - ref) / np.maximum(scale, 1e-30)) <= TOL_TC
 
 
 def test_check_result_harness(pkg, oracle):

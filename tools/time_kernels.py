@@ -106,6 +106,13 @@ def main():
         elif case == "c3csr":
             rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale)
             csr_case("c3_proteins_ideal", rp, ci, 128, flush)
+        elif case == "c3d":
+            # block-dense variant: every edge stays inside its community (what the dense part of a
+            # hybrid split looks like)
+            rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale, p_in=1.0)
+            val, B, C = csr_case("c3_proteins_pin1", rp, ci, 128, flush)
+            for bs in (16, 32):
+                bsr_case("c3_proteins_pin1", rp, ci, val, B, 128, bs, maths, flush)
         elif case == "c3":
             rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale)
             val, B, C = csr_case("c3_proteins_ideal", rp, ci, 128, flush)
