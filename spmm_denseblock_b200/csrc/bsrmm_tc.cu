@@ -15,17 +15,24 @@
 //   blocks per strip.  D lives in TMEM: lane = feature, column = row of A.
 //
 //   operand "A" of the MMA = B slab:   row-major B[k][ldb] read by TMA boxes of
-//       {32 features, bs rows}, SWIZZLE_128B  -> MN-major (feature-major) canonical layout
+//       {128 bytes of features, bs rows} -> MN-major (feature-major) canonical layout
+//       (bf16: SWIZZLE_128B; tf32: SWIZZLE_128B with 32-byte atoms, the only MN-major 32-bit layout)
 //   operand "B" of the MMA = A strip:  each bs x bs block is one TMA box {bs, bs} of
 //       bsr_val viewed as a [nnzb*bs][bs] matrix -> K-major (row-major blocks, DIR_ROW) or
 //       MN-major (column-major blocks, DIR_COLUMN) canonical layout, swizzle = row pitch
 //
-// Warp roles (192 threads, one persistent CTA per SM):
-//   warp 0      producer: pulls super-rows from a global counter, G-way merges the
-//               block rows' sorted column lists with warp votes, issues the TMA loads
-//   warp 1      MMA issuer (one elected lane): run detection, tcgen05.mma, tcgen05.commit
-//   warps 2..5  epilogue: tcgen05.ld of the finished accumulator, alpha/beta, stores to C
+// A pre-pass (bsr_plan_kernel, one warp per super-row) does the G-way merge of the block rows'
+// sorted column lists and leaves one 8-byte record {column block, presence mask} per step.
+//
+// Warp roles ((P + 5) warps; two CTAs per SM with 256 TMEM columns each when the accumulator fits,
+// so that one CTA's barrier round trips hide behind the other's MMAs):
+//   warps 0..P-1  producers: walk the plan, warp k % P fills step slot k: arms the stage's mbarrier
+//                 and issues the TMA loads (one 3-D box for the B slab, one box per present A block)
+//   warp P        MMA issuer (lane 0 issues): run detection, tcgen05.mma, tcgen05.commit
+//   warps P+1..   epilogue (4 warps = 128 TMEM lanes): tcgen05.ld, alpha/beta, stores to C
 // Two accumulator buffers in TMEM let the epilogue of super-row s overlap the MMAs of s+1.
+// Measured on B200 (profiles/r1c_bsr_tc_notes.md): the kernel is bound by the per-step latency of
+// the MMA-issuing warp (mbarrier wait + ~25 instructions per tcgen05.mma), not by HBM or the tensor pipe.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
@@ -35,7 +42,6 @@
 namespace spmmdb {
 namespace {
 
-constexpr int kThreads = 192;
 constexpr int kMaxStages = 8;
 constexpr uint32_t kEndFlag = 0x80000000u;  // step meta: end of a super-row
 
@@ -72,23 +78,20 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-          smem_u32(dst)),
-      "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
-      : "memory");
-}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
 
-__device__ __forceinline__ void tmem_alloc_512(uint32_t* slot) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(slot)) : "memory");
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, int cols) {  // cols: 256 (two CTAs per SM) or 512
+  if (cols == 256)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(slot)) : "memory");
+  else
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(slot)) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tmem_dealloc_512(uint32_t addr) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(addr) : "memory");
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, int cols) {
+  if (cols == 256) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(addr) : "memory");
+  else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(addr) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
@@ -125,25 +128,22 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout): start address,
-// leading / stride byte offsets in 16-byte units, version 1 (Blackwell), swizzle mode.
-__device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
-  uint64_t d = 0;
-  d |= (uint64_t)((addr >> 4) & 0x3fffu);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)layout << 61;
-  return d;
-}
+// Shared-memory matrix descriptors follow cute::UMMA::SmemDescriptor: bits 0-13 start address >> 4,
+// 16-29 leading byte offset >> 4, 32-45 stride byte offset >> 4, 46-47 version (1 = Blackwell),
+// 61-63 swizzle mode.
 constexpr uint32_t kLayoutSw128 = 2, kLayoutSw64 = 4, kLayoutSw32 = 6, kLayoutSw128B32 = 1;
 
 struct TcArgs {
   int mb, n, bs, G, NT, tiles, nchunks, stages;
   int dir, c_layout;
   int num_super;
+  int tmem_cols;          // 512 (one CTA per SM) or 256 (two CTAs per SM)
+  int dbg;                // developer timing experiments: 1 = no A loads, 2 = no B loads, 4 = no MMAs
+  int b_one;              // B slab fetched by one 3-D TMA box (n is a multiple of the chunk width)
   const int* rowptr;
   const int* colind;
+  const uint2* plan;      // step records {column block, presence mask}, super-row s starts at rowptr[s*G]
+  const int* plan_count;  // steps per super-row
   float* C;
   int64_t ldc;
   float alpha, beta;
@@ -164,11 +164,79 @@ struct __align__(8) TcSmemCtl {
   uint64_t tmem_empty[2];
   StepMeta meta[kMaxStages];
   AccInfo acc[2];
+  int srow[2];
   uint32_t tmem_base;
 };
 
-template <bool BF16>
-__global__ void __launch_bounds__(kThreads, 1)
+// ---------------------------------------------------------------------------------------
+// Plan: the G-way merge of a super-row's sorted column-block lists, done once per call by
+// one warp per super-row (thousands of warps in flight hide the index-load latency; inside
+// the MMA kernel the same merge would serialise on one producer warp).  Step t of super-row
+// s = the t-th distinct column block j of its block rows and the mask of block rows that
+// hold (i, j).  Records live at plan[rowptr[s*G] + t]: steps(s) <= blocks(s), no scan needed.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bsr_plan_kernel(int mb, int G, int num_super, const int* __restrict__ rowptr,
+                                                       const int* __restrict__ colind, uint2* __restrict__ plan,
+                                                       int* __restrict__ plan_count) {
+  constexpr int W = 8;
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int s = warp; s < num_super; s += nwarps) {
+    const int br = s * G + lane;
+    int cur = 0, end = 0;
+    if (lane < G && br < mb) { cur = __ldg(rowptr + br); end = __ldg(rowptr + br + 1); }
+    const int base = __shfl_sync(0xffffffffu, cur, 0);
+    int q[W];
+    bool refill = true;
+    int t = 0;
+    while (true) {
+      if (refill) {
+#pragma unroll
+        for (int i = 0; i < W; ++i) q[i] = (cur + i < end) ? __ldg(colind + cur + i) : 0x7fffffff;
+      }
+      const int col = q[0];
+      int jmin = col;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) jmin = min(jmin, __shfl_xor_sync(0xffffffffu, jmin, o));
+      if (jmin == 0x7fffffff) break;
+      const bool mine = (col == jmin);
+      const uint32_t present = __ballot_sync(0xffffffffu, mine);
+      if (lane == 0) plan[base + t] = make_uint2((uint32_t)jmin, present);
+      ++t;
+      if (mine) {
+        ++cur;
+#pragma unroll
+        for (int i = 0; i + 1 < W; ++i) q[i] = q[i + 1];
+        q[W - 1] = 0x7fffffff;
+      }
+      // a lane that advanced W times has an empty window: refill everybody together
+      refill = __any_sync(0xffffffffu, mine && (cur < end) && (q[0] == 0x7fffffff));
+    }
+    if (lane == 0) plan_count[s] = t;
+  }
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_addr(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_addr(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2,
+                                                 uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+          dst),
+      "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+
+template <bool BF16, int P>
+__global__ void __launch_bounds__((P + 5) * 32, 2)
 bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapA) {
   constexpr int ESIZE = BF16 ? 2 : 4;
   constexpr int FC = 128 / ESIZE;           // features per 128-byte chunk
@@ -179,7 +247,9 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
   // stage buffers first (1024-byte aligned for the 128B swizzle), control block after them
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   TcSmemCtl* ctl = (TcSmemCtl*)(smem + (size_t)a.stages * a.stage_bytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index broadcast from lane 0: the role dispatch below becomes a warp-uniform branch for the compiler,
+  // which lets the MMA / TMA operands live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.stages; ++i) { mbar_init(&ctl->full[i], 1); mbar_init(&ctl->empty[i], 1); }
@@ -188,82 +258,94 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
     tma_prefetch_desc(&mapB);
     tma_prefetch_desc(&mapA);
   }
-  if (warp == 2) tmem_alloc_512(&ctl->tmem_base);
+  if (warp == P + 1) tmem_alloc(&ctl->tmem_base, a.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
   const int acc_cols = a.tiles * a.NT;  // <= 256
 
-  if (warp == 0) {
-    // ===================== producer =====================
-    int stage = 0;
+  if (warp < P) {
+    // ===================== producers =====================
+    // All P warps walk the same step sequence; step slot k (counted over the CTA's whole life,
+    // end-of-super-row markers included) is filled by warp k % P into stage k % stages.
+    int stage = 0, own = 0;
     uint32_t phase = 0;
-    constexpr int W = 8;  // column-index look-ahead window per block row
+    int it = 0, s_next = 0;
+    if (warp == 0 && lane == 0) s_next = atomicAdd(a.counter, 1);
+    const uint32_t smem_base = smem_u32(smem);
+    long long dbg_wait = 0, dbg_steps = 0;
+    const long long dbg_t0 = clock64();
     while (true) {
-      int s = 0;
-      if (lane == 0) s = atomicAdd(a.counter, 1);
-      s = __shfl_sync(0xffffffffu, s, 0);
-      if (s >= a.num_super) {
+      if (warp == 0 && lane == 0) ctl->srow[it & 1] = s_next;
+      if (P > 1) named_bar_sync(1, 32 * P); else __syncwarp();
+      const int s = *(volatile int*)&ctl->srow[it & 1];
+      ++it;
+      const bool term = s >= a.num_super;
+      if (warp == 0 && lane == 0 && !term) s_next = atomicAdd(a.counter, 1);
+      int cnt = 0, base = 0, cur = 0;
+      if (!term) {
+        base = __ldg(a.rowptr + s * a.G);
+        cnt = __ldg(a.plan_count + s);
+        const int br = s * a.G + lane;
+        if (lane < a.G && br < a.mb) cur = __ldg(a.rowptr + br);
+      }
+      for (int t0 = 0; t0 < cnt; t0 += 32) {
+        uint2 rec = make_uint2(0u, 0u);
+        if (t0 + lane < cnt) rec = __ldg(a.plan + base + t0 + lane);
+        const int nt = min(32, cnt - t0);
+        for (int i = 0; i < nt; ++i) {
+          const int j = (int)__shfl_sync(0xffffffffu, rec.x, i);
+          const uint32_t mask = __shfl_sync(0xffffffffu, rec.y, i);
+          const bool mine = (mask >> lane) & 1u;
+          if (own == warp) {
+            const long long tw0 = (a.dbg & 32) ? clock64() : 0;
+            mbar_wait(&ctl->empty[stage], phase ^ 1);
+            if (a.dbg & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
+            uint64_t* fb = &ctl->full[stage];
+            const uint32_t sB = smem_base + (uint32_t)stage * a.stage_bytes;
+            if (lane == 0) {
+              ctl->meta[stage].mask = mask;
+              mbar_arrive_expect_tx(fb, ((a.dbg & 2) ? 0u : a.nchunks * a.chunk_bytes) +
+                                            ((a.dbg & 1) ? 0u : __popc(mask) * a.block_bytes));
+            }
+            __syncwarp();
+            if (a.dbg & 2) {
+            } else if (a.b_one) {
+              if (lane == 0) tma_load_3d_addr(sB, &mapB, 0, j * a.bs, 0, fb);
+            } else if (lane < a.nchunks) {
+              tma_load_2d_addr(sB + (uint32_t)lane * a.chunk_bytes, &mapB, lane * FC, j * a.bs, fb);
+            }
+            if (mine && !(a.dbg & 1)) tma_load_2d_addr(sB + a.stage_b_bytes + (uint32_t)lane * a.block_bytes, &mapA, 0, cur * a.bs, fb);
+          }
+          cur += mine ? 1 : 0;
+          if (++own == P) own = 0;
+          if (++stage == a.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+      // end of the super-row (s = -1: no more work)
+      if (own == warp) {
         mbar_wait(&ctl->empty[stage], phase ^ 1);
         if (lane == 0) {
           ctl->meta[stage].mask = kEndFlag;
-          ctl->meta[stage].s = -1;
+          ctl->meta[stage].s = term ? -1 : s;
           mbar_arrive(&ctl->full[stage]);
         }
-        break;
       }
-      const int br = s * a.G + lane;
-      int cur = 0, end = 0;
-      if (lane < a.G && br < a.mb) { cur = __ldg(a.rowptr + br); end = __ldg(a.rowptr + br + 1); }
-      int q[W];
-      int have = 0;  // valid look-ahead entries (same for every lane by construction)
-      while (true) {
-        if (have == 0) {
-#pragma unroll
-          for (int i = 0; i < W; ++i) q[i] = (cur + i < end) ? __ldg(a.colind + cur + i) : 0x7fffffff;
-          have = W;
-        }
-        const int col = q[0];
-        int jmin = col;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) jmin = min(jmin, __shfl_xor_sync(0xffffffffu, jmin, o));
-        if (jmin == 0x7fffffff) break;
-        const bool mine = (col == jmin);
-        const uint32_t present = __ballot_sync(0xffffffffu, mine);
-        mbar_wait(&ctl->empty[stage], phase ^ 1);
-        uint8_t* sB = smem + (size_t)stage * a.stage_bytes;
-        uint8_t* sA = sB + a.stage_b_bytes;
-        if (lane == 0) {
-          ctl->meta[stage].mask = present;
-          mbar_arrive_expect_tx(&ctl->full[stage], a.nchunks * a.chunk_bytes + __popc(present) * a.block_bytes);
-        }
-        __syncwarp();
-        if (lane < a.nchunks) tma_load_2d(sB + (size_t)lane * a.chunk_bytes, &mapB, lane * FC, jmin * a.bs, &ctl->full[stage]);
-        if (mine) {
-          tma_load_2d(sA + (size_t)lane * a.block_bytes, &mapA, 0, cur * a.bs, &ctl->full[stage]);
-          ++cur;
-#pragma unroll
-          for (int i = 0; i + 1 < W; ++i) q[i] = q[i + 1];
-          q[W - 1] = 0x7fffffff;
-        }
-        // a lane that advanced W times has an empty window: refill everybody together
-        const bool dry = mine && (cur < end) && (q[0] == 0x7fffffff);
-        have = __any_sync(0xffffffffu, dry) ? 0 : have;
-        if (++stage == a.stages) { stage = 0; phase ^= 1; }
-      }
-      // end of the super-row
-      mbar_wait(&ctl->empty[stage], phase ^ 1);
-      if (lane == 0) {
-        ctl->meta[stage].mask = kEndFlag;
-        ctl->meta[stage].s = s;
-        mbar_arrive(&ctl->full[stage]);
-      }
+      if (++own == P) own = 0;
       if (++stage == a.stages) { stage = 0; phase ^= 1; }
+      if (term) break;
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    if ((a.dbg & 32) && blockIdx.x == 0 && lane == 0)
+      printf("producer %d: total %lld cyc, own steps %lld, wait(empty) %lld cyc\n", warp, clock64() - dbg_t0, dbg_steps,
+             dbg_wait);
+  } else if (warp == P) {
+    // ===================== MMA issuer =====================
+    // The whole warp walks the loop so that addresses and descriptors stay warp-uniform (uniform
+    // registers feed tcgen05.mma without per-operand R2UR moves); lane 0 alone issues.
+    {
+      const bool leader = lane == 0;
+      const uint32_t tmem_base = __shfl_sync(0xffffffffu, ctl->tmem_base, 0);  // warp-uniform copy
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -273,64 +355,89 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       const uint32_t idesc_base = (1u << 4) | (FMT << 7) | (FMT << 10) | (1u << 15) |
                                   ((a.dir == SPMMDB_DIR_COLUMN ? 1u : 0u) << 16) | ((128u >> 4) << 24);
       const int ksteps = a.bs / KI;
+      const int max_run = 256 / a.bs;
+      // descriptor halves that never change (hi: SBO, version 1, swizzle mode; lo bits 16+: LBO)
+      // MMA operand A = B slab, MN-major: 128-byte feature chunks LBO apart, k groups SBO apart
+      //   bf16: SWIZZLE_128B, groups of 8 k rows (1024 B); tf32: 32-bit MN-major operands exist only in
+      //   the 128B-swizzle-with-32B-atoms layout, groups of 4 k rows (512 B)
+      const uint32_t a_hi = ((BF16 ? 1024u : 512u) >> 4) | (1u << 14) | ((BF16 ? kLayoutSw128 : kLayoutSw128B32) << 29);
+      const uint32_t a_lo_fixed = ((a.chunk_bytes >> 4) & 0x3fffu) << 16;
+      const uint32_t a_kstep = (uint32_t)(KI * 128) >> 4;  // KI rows of 128 B per k-step
+      // MMA operand B = A strip.  DIR_ROW: K-major, advance 32 B inside the swizzle atom per k-step,
+      //   8-row groups SBO = 8 * rp apart.  DIR_COLUMN: MN-major, blocks LBO apart, k groups 8 * rp apart.
+      const uint32_t b_hi = ((8u * rp) >> 4) | (1u << 14) | (a_layout << 29);
+      const uint32_t b_lo_fixed = (a.dir == SPMMDB_DIR_ROW ? 1u : ((a.block_bytes >> 4) & 0x3fffu)) << 16;
+      const uint32_t b_kstep = (a.dir == SPMMDB_DIR_ROW ? 32u : (uint32_t)KI * rp) >> 4;
+      const uint32_t smem_base = smem_u32(smem);
       bool done = false;
+      long long dbg_wait = 0, dbg_steps = 0, dbg_wait_acc = 0;
+      const long long dbg_t0 = clock64();
       while (!done) {
+        const long long ta0 = (a.dbg & 32) ? clock64() : 0;
         mbar_wait(&ctl->tmem_empty[acc], acc_phase[acc] ^ 1);
+        if (a.dbg & 32) dbg_wait_acc += clock64() - ta0;
         tc_fence_after();
         uint32_t touched = 0;
         while (true) {
+          const long long tw0 = (a.dbg & 32) ? clock64() : 0;
           mbar_wait(&ctl->full[stage], phase);
+          if (a.dbg & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
           tc_fence_after();
-          const uint32_t mask = ctl->meta[stage].mask;
+          // broadcast from lane 0: tells the compiler the value (and the control flow below) is warp-uniform
+          const uint32_t mask = __shfl_sync(0xffffffffu, ctl->meta[stage].mask, 0);
           if (mask & kEndFlag) {
-            const int s = ctl->meta[stage].s;
-            ctl->acc[acc].s = s;
-            ctl->acc[acc].touched = touched;
-            mbar_arrive(&ctl->tmem_full[acc]);  // release: publishes acc[] to the epilogue
-            umma_commit(&ctl->tmem_full[acc]);  // arrives when every MMA issued so far has completed
-            mbar_arrive(&ctl->empty[stage]);
+            const int s = __shfl_sync(0xffffffffu, ctl->meta[stage].s, 0);
+            if (leader) {
+              ctl->acc[acc].s = s;
+              ctl->acc[acc].touched = touched;
+              mbar_arrive(&ctl->tmem_full[acc]);  // release: publishes acc[] to the epilogue
+              umma_commit(&ctl->tmem_full[acc]);  // arrives when every MMA issued so far has completed
+              mbar_arrive(&ctl->empty[stage]);
+            }
+            __syncwarp();
             if (++stage == a.stages) { stage = 0; phase ^= 1; }
             if (s < 0) done = true;
             break;
           }
-          const uint32_t sB = smem_u32(smem + (size_t)stage * a.stage_bytes);
-          const uint32_t sA = sB + a.stage_b_bytes;
-          for (int t = 0; t < a.tiles; ++t) {
-            uint32_t m = mask;
-            while (m) {
-              const int l0 = __ffs(m) - 1;
-              const uint32_t tb = (touched >> l0) & 1u;
-              int len = 1;
-              while (l0 + len < a.G && ((m >> (l0 + len)) & 1u) && ((touched >> (l0 + len)) & 1u) == tb &&
-                     (len + 1) * a.bs <= 256)
-                ++len;
-              m &= ~(((1u << len) - 1u) << l0);
-              const uint32_t idesc = idesc_base | ((uint32_t)(len * a.bs) >> 3) << 17;
-              const uint32_t d = tmem_base + (uint32_t)(acc * acc_cols + t * a.NT + l0 * a.bs);
+          const uint32_t sB = smem_base + (uint32_t)stage * a.stage_bytes;
+          const uint32_t sA16 = (sB + a.stage_b_bytes) >> 4;
+          const uint32_t dcol = tmem_base + (uint32_t)(acc * acc_cols);
+          uint32_t m = (a.dbg & 4) ? 0u : mask;
+          while (m) {
+            const int l0 = __ffs(m) - 1;
+            const uint32_t tb = (touched >> l0) & 1u;
+            const int ones = __ffs(~(m >> l0)) - 1;                                   // present run length
+            const uint32_t diff = (tb ? ~touched : touched) >> l0;                    // touched status changes
+            const int same = diff ? __ffs(diff) - 1 : 32;
+            const int len = min(min(ones, same), max_run);
+            m &= ~((len >= 32 ? 0xffffffffu : ((1u << len) - 1u)) << l0);
+            const uint32_t idesc = idesc_base | (((uint32_t)(len * a.bs) >> 3) << 17);
+            const uint32_t b_lo0 = ((sA16 + (((uint32_t)l0 * a.block_bytes) >> 4)) & 0x3fffu) | b_lo_fixed;
+            for (int t = 0; t < a.tiles; ++t) {
+              const uint32_t d = dcol + (uint32_t)(t * a.NT + l0 * a.bs);
+              const uint32_t a_lo0 = (((sB + (uint32_t)(t * CPT) * a.chunk_bytes) >> 4) & 0x3fffu) | a_lo_fixed;
               for (int ks = 0; ks < ksteps; ++ks) {
-                // MMA operand A = B slab, MN-major SW128: 8 k-rows x 128 B per core group,
-                // feature chunks LBO apart, k groups SBO = 1024 B apart
-                // (tf32: MN-major 32-bit operands exist only in the 128B-swizzle-with-32B-atoms layout,
-                //  whose k groups are 4 rows = 512 B)
-                const uint64_t adesc = smem_desc(sB + (uint32_t)(t * CPT) * a.chunk_bytes + (uint32_t)ks * KI * 128u,
-                                                 a.chunk_bytes, BF16 ? 1024u : 512u, BF16 ? kLayoutSw128 : kLayoutSw128B32);
-                uint64_t bdesc;
-                if (a.dir == SPMMDB_DIR_ROW)  // K-major: advance inside the swizzle atom by 32 B per k-step
-                  bdesc = smem_desc(sA + (uint32_t)l0 * a.block_bytes + (uint32_t)ks * 32u, 16u, 8u * rp, a_layout);
-                else  // MN-major: blocks (n chunks) LBO apart, k groups of 8 rows SBO apart
-                  bdesc = smem_desc(sA + (uint32_t)l0 * a.block_bytes + (uint32_t)ks * KI * rp, a.block_bytes, 8u * rp,
-                                    a_layout);
-                umma<BF16>(d, adesc, bdesc, idesc, (tb | (ks > 0)) ? 1u : 0u);
+                const uint64_t adesc = ((uint64_t)a_hi << 32) | (a_lo0 + (uint32_t)ks * a_kstep);
+                const uint64_t bdesc = ((uint64_t)b_hi << 32) | (b_lo0 + (uint32_t)ks * b_kstep);
+                // tcgen05.mma has per-thread semantics: exactly one lane may issue it
+                if (leader) umma<BF16>(d, adesc, bdesc, idesc, (tb | (ks > 0)) ? 1u : 0u);
               }
             }
           }
           touched |= mask;
-          umma_commit(&ctl->empty[stage]);  // frees the stage when these MMAs have read it
+          if (leader) {
+            if (a.dbg & 8) mbar_arrive(&ctl->empty[stage]);
+            else umma_commit(&ctl->empty[stage]);  // frees the stage when these MMAs have read it
+          }
+          __syncwarp();
           if (++stage == a.stages) { stage = 0; phase ^= 1; }
         }
         acc_phase[acc] ^= 1;
         acc ^= 1;
       }
+      if ((a.dbg & 32) && blockIdx.x == 0 && lane == 0)
+        printf("mma: total %lld cyc, steps %lld, wait(full) %lld cyc, wait(tmem_empty) %lld cyc\n", clock64() - dbg_t0,
+               dbg_steps, dbg_wait, dbg_wait_acc);
     }
   } else {
     // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
@@ -338,6 +445,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
     int acc = 0;
     uint32_t full_phase[2] = {0, 0};
     const int64_t m_rows = (int64_t)a.mb * a.bs;
+    const int cpb = 32 / a.bs;  // block rows per 32 accumulator columns (0 when bs = 64)
     while (true) {
       mbar_wait(&ctl->tmem_full[acc], full_phase[acc]);
       tc_fence_after();
@@ -351,37 +459,38 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
           const int64_t row0 = (int64_t)s * a.NT + c0;
           if (row0 >= m_rows) break;
           uint32_t v[32];
-          // block rows covered by these 32 columns
-          const int lb = c0 / a.bs, le = (c0 + 31) / a.bs;
-          uint32_t any = 0;
-          for (int l = lb; l <= le; ++l) any |= (touched >> l) & 1u;
-          if (any) {
-            tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(acc * acc_cols + t * a.NT + c0), v);
-          }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int l = (c0 + j) / a.bs;
-            if (!any || !((touched >> l) & 1u)) v[j] = 0u;
-          }
-          if (!fok) continue;
-          if (a.c_layout == SPMMDB_ROW_MAJOR) {
-            float* __restrict__ cp = a.C + row0 * a.ldc + f;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (row0 + j < m_rows) {
-                float o = a.alpha * __uint_as_float(v[j]);
-                if (a.beta != 0.f) o = fmaf(a.beta, cp[(int64_t)j * a.ldc], o);
-                cp[(int64_t)j * a.ldc] = o;
-              }
-            }
+          // block rows covered by these 32 columns: 2 (bs 16), 1 (bs 32) or half of one (bs 64)
+          uint32_t tmask;  // bit j set = column j belongs to a block row that received an MMA
+          if (cpb == 2) {
+            const uint32_t tt = (touched >> (c0 / 16)) & 3u;
+            tmask = ((tt & 1u) ? 0x0000ffffu : 0u) | ((tt & 2u) ? 0xffff0000u : 0u);
+          } else if (cpb == 1) {
+            tmask = ((touched >> (c0 / 32)) & 1u) ? 0xffffffffu : 0u;
           } else {
-            float* __restrict__ cp = a.C + (int64_t)f * a.ldc + row0;
+            tmask = ((touched >> (c0 / 64)) & 1u) ? 0xffffffffu : 0u;
+          }
+          if (tmask) tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(acc * acc_cols + t * a.NT + c0), v);
+          if (tmask != 0xffffffffu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (!((tmask >> j) & 1u)) v[j] = 0u;
+          }
+          if (!fok || (a.dbg & 16)) continue;
+          const int nrow = (int)min((int64_t)32, m_rows - row0);
+          float* __restrict__ cp;
+          int64_t cs;  // stride between consecutive rows of A in C
+          if (a.c_layout == SPMMDB_ROW_MAJOR) { cp = a.C + row0 * a.ldc + f; cs = a.ldc; }
+          else { cp = a.C + (int64_t)f * a.ldc + row0; cs = 1; }
+          if (nrow == 32 && a.beta == 0.f) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) cp[(int64_t)j * cs] = a.alpha * __uint_as_float(v[j]);
+          } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (row0 + j < m_rows) {
+              if (j < nrow) {
                 float o = a.alpha * __uint_as_float(v[j]);
-                if (a.beta != 0.f) o = fmaf(a.beta, cp[j], o);
-                cp[j] = o;
+                if (a.beta != 0.f) o = fmaf(a.beta, cp[(int64_t)j * cs], o);
+                cp[(int64_t)j * cs] = o;
               }
             }
           }
@@ -397,7 +506,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc_512(tmem_base);
+  if (warp == P + 1) tmem_dealloc(tmem_base, a.tmem_cols);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -496,6 +605,33 @@ bool make_map_2d(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, 
   return r == CUDA_SUCCESS;
 }
 
+// B slab as ONE box: view row-major B[krows][ld] as (fc features, krows rows, n / fc chunks) with the chunk
+// dimension 128 bytes apart; box = {fc, bs, chunks} lands chunk-major in shared memory.
+bool make_map_b3d(CUtensorMap* map, bool bf16, const void* base, uint64_t fc, uint64_t krows, uint64_t chunks,
+                  uint64_t row_bytes, uint32_t bs) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[3] = {fc, krows, chunks};
+  cuuint64_t strides[2] = {row_bytes, 128};
+  cuuint32_t box[3] = {(cuuint32_t)fc, bs, (cuuint32_t)chunks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  bf16 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+template <bool BF16, int P>
+int launch_tc(const TcArgs& a, const CUtensorMap& mapB, const CUtensorMap& mapA, int grid, size_t smem_bytes,
+              cudaStream_t st) {
+  SPMMDB_CUDA_OK(cudaFuncSetAttribute(bsrmm_tc_kernel<BF16, P>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)smem_bytes));
+  bsrmm_tc_kernel<BF16, P><<<grid, (P + 5) * 32, smem_bytes, st>>>(a, mapB, mapA);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
 }  // namespace
 
 // Shapes the tensor-core kernel takes; everything else runs the fp32 CUDA-core kernel.
@@ -579,12 +715,21 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   TcArgs a;
   a.mb = mb; a.n = n; a.bs = bs; a.tiles = tiles; a.nchunks = nchunks;
   static const int nt_env = [] { const char* e = getenv("SPMMDB_BSR_NT"); return e ? atoi(e) : 0; }();
-  int NT = tiles <= 2 ? 128 : 64;
+  // Two CTAs per SM (256 TMEM columns and half the shared memory each) hide the per-step latency of
+  // the single MMA-issuing warp; they need tiles * NT <= 128 per accumulator buffer.
+  static const int cps_env = [] { const char* e = getenv("SPMMDB_BSR_CTAS_PER_SM"); return e ? atoi(e) : 0; }();
+  int cps = (cps_env == 1 || cps_env == 2) ? cps_env : (tiles == 1 ? 2 : 1);
+  if (tiles > 2 || (128 / tiles) < bs) cps = 1;
+  const int acc_max = cps == 2 ? 128 : 256;  // accumulator columns per buffer (two buffers)
+  int NT = 256;
   if (nt_env == 64 || nt_env == 128 || nt_env == 256) NT = nt_env;
-  while (NT * tiles > 256) NT >>= 1;
+  while (NT * tiles > acc_max) NT >>= 1;
   if (NT < bs) return SPMMDB_ERR_NOT_SUPPORTED;  // bs = 64 with > 4 tiles cannot happen (n <= 512)
+  a.tmem_cols = cps == 2 ? 256 : 512;
   a.NT = NT;
   a.G = NT / bs;
+  static const int dbg_env = [] { const char* e = getenv("SPMMDB_BSR_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+  a.dbg = dbg_env;
   a.dir = dir; a.c_layout = c_layout;
   a.num_super = (mb + a.G - 1) / a.G;
   a.rowptr = rowptr; a.colind = colind; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
@@ -594,36 +739,58 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   a.stage_b_bytes = (uint32_t)(tiles * cpt) * a.chunk_bytes;
   a.stage_bytes = (a.stage_b_bytes + (uint32_t)(NT * bs * esize) + 1023u) & ~1023u;
   const size_t ctl_bytes = sizeof(TcSmemCtl) + 64;
-  const size_t smem_max = 227 * 1024;
+  const size_t smem_max = cps == 2 ? 113 * 1024 : 227 * 1024;
   int stages = (int)((smem_max - 1024 - ctl_bytes) / a.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return SPMMDB_ERR_NOT_SUPPORTED;
   a.stages = stages;
   const size_t smem_bytes = 1024 + (size_t)stages * a.stage_bytes + ctl_bytes;
 
-  int* counter = (int*)scratch(kScratchBsr, 256, st);
-  if (counter == nullptr) return SPMMDB_ERR_ALLOC;
-  SPMMDB_CUDA_OK(cudaMemsetAsync(counter, 0, 4, st));
-  a.counter = counter;
+  // scratch: [0] super-row counter | plan_count[num_super] | plan[nnzb] (8-byte records)
+  const size_t off_count = 256;
+  const size_t off_plan = (off_count + sizeof(int) * (size_t)a.num_super + 255) & ~(size_t)255;
+  char* sc = (char*)scratch(kScratchBsr, off_plan + sizeof(uint2) * (size_t)nnzb, st);
+  if (sc == nullptr) return SPMMDB_ERR_ALLOC;
+  SPMMDB_CUDA_OK(cudaMemsetAsync(sc, 0, 4, st));
+  a.counter = (int*)sc;
+  a.plan_count = (const int*)(sc + off_count);
+  a.plan = (const uint2*)(sc + off_plan);
+  {
+    const int warps = a.num_super;
+    const int blocks = (warps + 7) / 8;
+    bsr_plan_kernel<<<blocks, 256, 0, st>>>(mb, a.G, a.num_super, rowptr, colind, (uint2*)(sc + off_plan),
+                                            (int*)(sc + off_count));
+    SPMMDB_CUDA_OK(cudaGetLastError());
+  }
 
   CUtensorMap mapB, mapA;
-  if (!make_map_2d(&mapB, bf16, Bt, (uint64_t)n, (uint64_t)krows, (uint64_t)ldbt * esize, (uint32_t)fc, (uint32_t)bs, bf16 ? 128 : 129))
+  a.b_one = (n % fc == 0) ? 1 : 0;
+  static const int b3d_env = [] { const char* e = getenv("SPMMDB_BSR_B3D"); return e ? atoi(e) : 1; }();
+  if (!b3d_env) a.b_one = 0;
+  if (a.b_one && !make_map_b3d(&mapB, bf16, Bt, (uint64_t)fc, (uint64_t)krows, (uint64_t)nchunks,
+                               (uint64_t)ldbt * esize, (uint32_t)bs))
+    a.b_one = 0;  // driver refused the overlapping view: one box per 128-byte chunk instead
+  if (!a.b_one && !make_map_2d(&mapB, bf16, Bt, (uint64_t)n, (uint64_t)krows, (uint64_t)ldbt * esize, (uint32_t)fc,
+                          (uint32_t)bs, bf16 ? 128 : 129))
     return SPMMDB_ERR_INVALID_VALUE;
   if (!make_map_2d(&mapA, bf16, At, (uint64_t)bs, (uint64_t)nnzb * bs, (uint64_t)bs * esize, (uint32_t)bs, (uint32_t)bs,
                    (uint32_t)(bs * esize)))
     return SPMMDB_ERR_INVALID_VALUE;
 
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
-  const int grid = a.num_super < nsm ? a.num_super : nsm;
+  const int grid = a.num_super < nsm * cps ? a.num_super : nsm * cps;
+  static const int p_env = [] { const char* e = getenv("SPMMDB_BSR_PRODUCERS"); return e ? atoi(e) : 0; }();
+  const int P = p_env >= 1 && p_env <= 4 ? p_env : 3;
   if (bf16) {
-    SPMMDB_CUDA_OK(cudaFuncSetAttribute(bsrmm_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    bsrmm_tc_kernel<true><<<grid, kThreads, smem_bytes, st>>>(a, mapB, mapA);
-  } else {
-    SPMMDB_CUDA_OK(cudaFuncSetAttribute(bsrmm_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    bsrmm_tc_kernel<false><<<grid, kThreads, smem_bytes, st>>>(a, mapB, mapA);
+    if (P == 1) return launch_tc<true, 1>(a, mapB, mapA, grid, smem_bytes, st);
+    if (P == 2) return launch_tc<true, 2>(a, mapB, mapA, grid, smem_bytes, st);
+    if (P == 4) return launch_tc<true, 4>(a, mapB, mapA, grid, smem_bytes, st);
+    return launch_tc<true, 3>(a, mapB, mapA, grid, smem_bytes, st);
   }
-  SPMMDB_CUDA_OK(cudaGetLastError());
-  return SPMMDB_OK;
+  if (P == 1) return launch_tc<false, 1>(a, mapB, mapA, grid, smem_bytes, st);
+  if (P == 2) return launch_tc<false, 2>(a, mapB, mapA, grid, smem_bytes, st);
+  if (P == 4) return launch_tc<false, 4>(a, mapB, mapA, grid, smem_bytes, st);
+  return launch_tc<false, 3>(a, mapB, mapA, grid, smem_bytes, st);
 }
 
 }  // namespace spmmdb
