@@ -186,7 +186,7 @@ def main():
     val = torch.ones(nnz, device=dev)  # unit adjacency weights (run_csrmm.cu:66)
     g = torch.Generator(device=dev).manual_seed(1234)
     B = torch.rand(n, K, generator=g, device=dev) * 2 - 1  # U(-1,1) (load_data.cc:29-40)
-    ranges = shard.nnz_balanced_ranges(rp, world)
+    ranges = shard.shard_plan(rp, world)  # C ABI: spmmdb_shard_plan
     lo, hi = ranges[rank]
     rps, cis, vals = shard.shard_csr(rp, ci, val, lo, hi)
     ms_, nnzs = hi - lo, cis.numel()
@@ -241,9 +241,7 @@ def main():
             barrier()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             s.record()
-            works = [dist.broadcast(B[l:h], src=g_, async_op=True) for g_, (l, h) in enumerate(ranges) if h > l]
-            for w in works:
-                w.wait()
+            shard.allgather_rows(B, ranges)
             e.record()
             barrier()
             tt = torch.tensor([s.elapsed_time(e)], device=dev, dtype=torch.float64)

@@ -142,6 +142,21 @@ int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr,
                           const float* h_val, const float* h_B, float* h_C, float alpha, float beta,
                           void* stream);
 
+/* --------------------------------------------------------------------------
+ * Multi-GPU row sharding (new behaviour defined by BASELINE.json; the reference
+ * is single-GPU).  HOST function, no CUDA call: splits the rows of a CSR (or
+ * block rows of a BSR) matrix into `parts` contiguous ranges of ~equal nnz.
+ *   h_rowptr  HOST pointer, m + 1 entries
+ *   align     boundaries are multiples of `align` rows (1 for CSR; the block size
+ *             when a CSR matrix is cut before csr2bsr)
+ *   bounds    HOST out, parts + 1 entries: range g = [bounds[g], bounds[g+1]);
+ *             boundary g = first row r with rowptr[r] >= g*nnz/parts, rounded down to `align`
+ * Output rows are disjoint, so the sharded SpMM needs no reduction; the long-row
+ * split of spmmdb_csrmm_f32 depends only on the row, so concatenated shards are
+ * bit-identical to the single-GPU result.
+ * ------------------------------------------------------------------------ */
+int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,6 +30,7 @@ SIGNATURES = {
     "spmmdb_csrmm_host_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, vp, C.c_float, C.c_float, vp],
     "spmmdb_set_bsrmm_math": [C.c_int],
     "spmmdb_get_bsrmm_math": [],
+    "spmmdb_shard_plan": [vp, C.c_int, C.c_int, C.c_int, vp],
     "spmmdb_version": [],
     "spmmdb_last_error": [],
     "spmmdb_device_sm": [],

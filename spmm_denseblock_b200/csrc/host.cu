@@ -39,3 +39,23 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
   return SPMMDB_OK;
 }
+
+extern "C" int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds) {
+  if (h_rowptr == nullptr || bounds == nullptr || m < 0 || parts < 1 || align < 1) return SPMMDB_ERR_INVALID_VALUE;
+  const int64_t nnz = h_rowptr[m];
+  bounds[0] = 0;
+  for (int g = 1; g < parts; ++g) {
+    const int64_t target = (int64_t)g * nnz / parts;
+    // first row with rowptr[row] >= target (lower bound)
+    int lo = 0, hi = m;
+    while (lo < hi) {
+      const int mid = lo + (hi - lo) / 2;
+      if (h_rowptr[mid] >= target) hi = mid; else lo = mid + 1;
+    }
+    int b = (lo / align) * align;
+    if (b < bounds[g - 1]) b = bounds[g - 1];
+    bounds[g] = b;
+  }
+  bounds[parts] = m;
+  return SPMMDB_OK;
+}

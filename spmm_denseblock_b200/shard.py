@@ -22,3 +22,32 @@ def shard_csr(rowptr, colind, val, lo, hi):
     s, e = int(rowptr[lo].item()), int(rowptr[hi].item())
     rp = (rowptr[lo:hi + 1] - rowptr[lo]).contiguous()
     return rp, colind[s:e].contiguous(), (val[s:e].contiguous() if val is not None else None)
+
+
+def shard_plan(rowptr, parts, align=1):
+    """Same ranges through the C ABI (spmmdb_shard_plan: host function, no CUDA call)."""
+    import ctypes as C
+
+    import numpy as np
+
+    from ._lib import lib, check
+    rp = np.ascontiguousarray(rowptr.detach().cpu().numpy() if hasattr(rowptr, "detach") else rowptr, dtype=np.int32)
+    bounds = np.zeros(parts + 1, np.int32)
+    check(lib().spmmdb_shard_plan(rp.ctypes.data_as(C.c_void_p), rp.size - 1, parts, align,
+                                  bounds.ctypes.data_as(C.c_void_p)), "spmmdb_shard_plan")
+    return [(int(bounds[g]), int(bounds[g + 1])) for g in range(parts)]
+
+
+def allgather_rows(B, ranges, group=None):
+    """Replicate B when rank g owns rows ranges[g] of it (e.g. the C rows it produced as the previous
+    layer's output): an all-gather-v as one broadcast per owner, in place into the full-size B.
+    Row counts differ per rank (nnz-balanced ranges), which rules out a plain all_gather.
+    Works on NCCL (device tensors, NVLink) and gloo (CPU tests)."""
+    import torch.distributed as dist
+    works = []
+    for g, (lo, hi) in enumerate(ranges):
+        if hi > lo:
+            works.append(dist.broadcast(B[lo:hi], src=g, group=group, async_op=True))
+    for w in works:
+        w.wait()
+    return B
