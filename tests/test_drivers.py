@@ -1,0 +1,126 @@
+"""The drop-in drivers (drivers/*.cu) keep the reference's command lines, file formats and printed
+lines and agree with the vendor library where the reference compared against it."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "drivers", "bin")
+PROGS = ["run_csrmm", "run_bsrmm", "test_csrmm", "test_bsrmm", "check_result", "csr2bsr", "bsr2csr", "block_cublas"]
+
+
+def _build():
+    import __graft_entry__ as g
+    if not all(os.path.exists(os.path.join(BIN, p)) for p in PROGS):
+        g.build()
+
+
+def test_drivers_build_and_link():
+    _build()
+    for p in PROGS:
+        exe = os.path.join(BIN, p)
+        assert os.access(exe, os.X_OK), exe
+        out = subprocess.run(["ldd", exe], capture_output=True, text=True).stdout
+        assert "libspmmdb.so" in out and "not found" not in out.split("libspmmdb.so")[1].splitlines()[0]
+
+
+def _run(args, cwd, env=None):
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run(args, cwd=cwd, capture_output=True, text=True, timeout=600, env=e)
+    return r.returncode, r.stdout + r.stderr
+
+
+def _checksum(out):
+    return float(re.search(r"checksum: (\S+)", out).group(1))
+
+
+@pytest.fixture(scope="module")
+def graph_dir(tmp_path_factory):
+    """tmp/<graph>_indptr.txt / _indices.txt in the reference's text format (load_data.cc:125-141)."""
+    from helpers import random_csr
+    d = tmp_path_factory.mktemp("drv")
+    os.makedirs(d / "tmp")
+    rng = np.random.default_rng(9)
+    rp, ci, _ = random_csr(rng, 3000, 3000, 11, hubs={3: 1200}, values="unit")
+    with open(d / "tmp" / "toy_indptr.txt", "w") as f:
+        f.write(f"{rp.size}\n" + " ".join(map(str, rp.tolist())))
+    with open(d / "tmp" / "toy_indices.txt", "w") as f:
+        f.write(f"{ci.size}\n" + " ".join(map(str, ci.tolist())))
+    return str(d), rp.size - 1, ci.size
+
+
+@pytest.mark.gpu
+def test_run_csrmm_cli_and_agreement(graph_dir):
+    _build()
+    cwd, n, nnz = graph_dir
+    sums = {}
+    for impl, tb in (("gespmm", 1), ("cusparseScsrmm2", 1), ("cusparseScsrmm2", 0), ("cusparseScsrmm", 0),
+                     ("cusparseSpMM", 1)):
+        rc, out = _run([os.path.join(BIN, "run_csrmm"), "toy", "128", impl, str(tb)], cwd)
+        assert rc == 0, out
+        assert f"graph = toy dim = 128 csrmmImpl = {impl} transposeB = {tb}" in out
+        assert f"n={n} nnz={nnz}" in out
+        assert len(re.findall(r"csrmm cost time:  \d+\.\d{10} ms", out)) == 10
+        assert re.search(r"average csrmm cost time: \d+\.\d{10} ms", out)
+        sums[(impl, tb)] = _checksum(out)
+    # same seeded B for every run: row-major runs agree with each other and with the vendor library
+    base = sums[("gespmm", 1)]
+    assert abs(sums[("cusparseScsrmm2", 1)] - base) <= 1e-3 * max(1.0, abs(base))
+    assert abs(sums[("cusparseSpMM", 1)] - base) <= 1e-3 * max(1.0, abs(base))
+    assert abs(sums[("cusparseScsrmm2", 0)] - sums[("cusparseScsrmm", 0)]) <= 1e-6 * max(1.0, abs(base))
+
+
+@pytest.mark.gpu
+def test_run_bsrmm_cli_and_agreement(graph_dir):
+    _build()
+    cwd, n, nnz = graph_dir
+    for bs in (4, 16):
+        sums = {}
+        for impl, math in (("cusparse", "fp32"), ("rocsparse", "fp32"), ("rocsparse", "tf32")):
+            rc, out = _run([os.path.join(BIN, "run_bsrmm"), "toy", str(bs), "64", impl], cwd, {"SPMMDB_BSRMM_MATH": math})
+            assert rc == 0, out
+            assert "tmp/toy" in out and f"n={n} nnz={nnz}" in out
+            assert re.search(r"numVal = \d+", out) and re.search(r"density:  \d+\.\d{10}", out)
+            assert re.search(r"bsrmm cost time:  \d+\.\d{10} ms", out)
+            sums[(impl, math)] = _checksum(out)
+        ref = sums[("cusparse", "fp32")]
+        assert abs(sums[("rocsparse", "fp32")] - ref) <= 1e-3 * max(1.0, abs(ref))
+        assert abs(sums[("rocsparse", "tf32")] - ref) <= 2e-2 * max(1.0, abs(ref)) + 1.0
+
+
+@pytest.mark.gpu
+def test_check_result_and_conversion_drivers(tmp_path):
+    _build()
+    rc, out = _run([os.path.join(BIN, "check_result"), "8192", "0.01", "64"], str(tmp_path))
+    assert rc == 0 and "all checks passed" in out, out
+    rc, out = _run([os.path.join(BIN, "csr2bsr"), "0.1"], str(tmp_path))
+    assert rc == 0 and "PASSED" in out, out
+    rc, out = _run([os.path.join(BIN, "bsr2csr"), "0.05", "4"], str(tmp_path))
+    assert rc == 0 and "PASSED" in out, out
+    for math in ("fp32", "tf32"):
+        rc, out = _run([os.path.join(BIN, "block_cublas")], str(tmp_path), {"SPMMDB_BSRMM_MATH": math})
+        assert rc == 0 and "PASSED" in out, out
+
+
+@pytest.mark.gpu
+def test_microbench_drivers_print_reference_lines(tmp_path):
+    _build()
+    rc, out = _run([os.path.join(BIN, "test_csrmm"), "0.0001", "64", "gespmm"], str(tmp_path))
+    assert rc == 0 and re.search(r"csrmm cost time: \d+\.\d{10} ms\nGFLOPs: \d+\.\d{10}", out), out
+    s1 = _checksum(out)
+    rc, out = _run([os.path.join(BIN, "test_csrmm"), "0.0001", "64", "cusparse"], str(tmp_path))
+    assert rc == 0, out
+    assert abs(_checksum(out) - s1) <= 1e-3 * max(1.0, abs(s1))
+    for tb in (0, 1):
+        sums = []
+        for impl in ("rocsparse", "cusparse"):
+            rc, out = _run([os.path.join(BIN, "test_bsrmm"), "0.0005", "16", "64", impl, str(tb)], str(tmp_path))
+            assert rc == 0 and re.search(r"bsrmm cost time: \d+\.\d{10} ms\nGFLOPs: \d+\.\d{10}", out), out
+            sums.append(_checksum(out))
+        assert abs(sums[0] - sums[1]) <= 1e-3 * max(1.0, abs(sums[1]))
+    rc, out = _run([os.path.join(BIN, "test_block_cublas"), "0.0005", "16", "64"], str(tmp_path))
+    assert rc == 0 and "block gemm cost time" in out, out
