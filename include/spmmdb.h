@@ -133,6 +133,29 @@ int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr, const int
                        float* csr_val, void* stream);
 
 /* --------------------------------------------------------------------------
+ * Hybrid dense-block split: replaces divide_matrix (divide.cu:52-127), the CPU
+ * pre-pass of the reference's `divide` driver.  Per block row, every column
+ * block whose fill (float)(count * 1.0 / bs^2) >= density becomes a BSR block
+ * (ascending block columns, zero filled); every other non-zero stays, in its
+ * original order, in a remainder CSR matrix of the same shape.  A = A_bsr +
+ * A_csr, so  C = A_csr * B  then  C += A_bsr * B  (divide.cu:348-373: both calls
+ * with beta = 1 into a zeroed C) is the whole product, with the dense part on
+ * the tensor-core BSR path and the rest on the CSR path.
+ *   val      NULL = unit weights (the reference stores 1.0f, divide.cu:113,230)
+ *   density  empty blocks never qualify (the reference emits them for density <= 0)
+ * Two phases like csr2bsr: _nnz writes both row-pointer arrays (device) and
+ * returns nnzb / the remainder nnz through HOST pointers (synchronises), the
+ * caller allocates, _f32 fills.  spmmdb_divide_threshold = the smallest count
+ * per block that qualifies (host function, no CUDA).
+ * ------------------------------------------------------------------------ */
+int spmmdb_divide_threshold(int block_dim, float density);
+int spmmdb_divide_nnz(int m, int n, const int* rowptr, const int* colind, int block_dim, float density,
+                      int* bsr_rowptr, int* csr_rowptr, int* nnzb_host, int* csr_nnz_host, void* stream);
+int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const int* colind, const float* val,
+                      int block_dim, float density, const int* bsr_rowptr, int* bsr_colind, float* bsr_val,
+                      const int* csr_rowptr, int* csr_colind, float* csr_val, void* stream);
+
+/* --------------------------------------------------------------------------
  * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all
  * pointers are HOST pointers (pinned memory gives full PCIe rate).  Copies A and
  * B to the device, runs the device path, copies C back and synchronises -- the

@@ -221,6 +221,170 @@ __global__ void __launch_bounds__(256) bsr2csr_kernel(int dir, int mb, int bs, c
   }
 }
 
+// ---- hybrid dense-block split (divide.cu:52-127 divide_matrix) -------------------
+// Same bs-way merge as csr2bsr, one warp per block row, but every column block is
+// first COUNTED (the rows are ascending, so a lane's entries of block b are the run
+// below column (b + 1) * bs) and only blocks with count >= thr are emitted as BSR
+// blocks; the entries of the other blocks go, in their original order, to the
+// remainder CSR (lane l owns row l of the block row, so a row's remainder is written
+// by one lane, front to back).  thr is the smallest count whose fill
+// (float)(count * 1.0 / bs^2) reaches the caller's density, found on the host with
+// the reference's own expression (divide.cu:89-93), so the dense / sparse decision is
+// the reference's bit for bit.
+// MODE 0: counts (blocks per block row, remainder entries per row).  MODE 1: fill.
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int R, int MODE>
+__global__ void __launch_bounds__(kWarpsPerCta * 32) divide_kernel(
+    int dir, int m, int mb, int bs, int thr, const int* __restrict__ rowptr, const int* __restrict__ colind,
+    const float* __restrict__ val, int* __restrict__ bsr_counts, int* __restrict__ csr_counts,
+    const int* __restrict__ bsr_rowptr, int* __restrict__ bsr_colind, float* __restrict__ bsr_val,
+    const int* __restrict__ csr_rowptr, int* __restrict__ csr_colind, float* __restrict__ csr_val,
+    int warps_per_cta) {
+  extern __shared__ float smem[];
+  const int lane = threadIdx.x & 31;
+  const int wid = threadIdx.x >> 5;
+  if (wid >= warps_per_cta) return;
+  const int bs2 = bs * bs;
+  float* tile = smem + (size_t)wid * bs2;
+  if (MODE == 1) {
+    for (int i = lane; i < bs2; i += 32) tile[i] = 0.f;
+    __syncwarp();
+  }
+  for (int ib = blockIdx.x * warps_per_cta + wid; ib < mb; ib += gridDim.x * warps_per_cta) {
+    int p[R], e[R], head[R], rem[R];
+#pragma unroll
+    for (int t = 0; t < R; ++t) {
+      const int r = lane + 32 * t;
+      const int row = ib * bs + r;
+      p[t] = 0; e[t] = 0;
+      if (r < bs && row < m) { p[t] = __ldg(rowptr + row); e[t] = __ldg(rowptr + row + 1); }
+      head[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) / bs : INT_MAX;
+      rem[t] = (MODE == 1 && r < bs && row < m) ? __ldg(csr_rowptr + row) : 0;  // MODE 1: next output slot
+    }
+    const int64_t base = (MODE == 0) ? 0 : __ldg(bsr_rowptr + ib);
+    int step = 0;
+    while (true) {
+      int mymin = head[0];
+#pragma unroll
+      for (int t = 1; t < R; ++t) mymin = min(mymin, head[t]);
+      const int bmin = warp_min(mymin);
+      if (bmin == INT_MAX) break;
+      const int col0 = bmin * bs;
+      const int64_t lim = (int64_t)col0 + bs;  // first column past the block
+      int q[R], mycnt = 0;
+#pragma unroll
+      for (int t = 0; t < R; ++t) {
+        q[t] = p[t];
+        if (head[t] == bmin) {
+          while (q[t] < e[t] && __ldg(colind + q[t]) < lim) ++q[t];
+          mycnt += q[t] - p[t];
+        }
+      }
+      const bool dense = warp_sum(mycnt) >= thr;
+      if (MODE == 0) {
+        if (dense) ++step;
+        else {
+#pragma unroll
+          for (int t = 0; t < R; ++t) rem[t] += q[t] - p[t];
+        }
+      } else if (dense) {
+        float* out = bsr_val + (base + step) * bs2;
+#pragma unroll
+        for (int t = 0; t < R; ++t) {
+          const int r = lane + 32 * t;
+          for (int i = p[t]; i < q[t]; ++i) {
+            const int c = __ldg(colind + i) - col0;
+            tile[(dir == SPMMDB_DIR_ROW) ? r * bs + c : c * bs + r] = val ? __ldg(val + i) : 1.0f;
+          }
+        }
+        __syncwarp();
+        if ((bs2 & 3) == 0) {
+          float4* o4 = reinterpret_cast<float4*>(out);
+          float4* t4 = reinterpret_cast<float4*>(tile);
+          for (int i = lane; i < bs2 / 4; i += 32) {
+            __stcs(o4 + i, t4[i]);
+            t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        } else {
+          for (int i = lane; i < bs2; i += 32) { out[i] = tile[i]; tile[i] = 0.f; }
+        }
+        __syncwarp();
+        if (lane == 0) bsr_colind[base + step] = bmin;
+        ++step;
+      } else {
+#pragma unroll
+        for (int t = 0; t < R; ++t) {
+          for (int i = p[t]; i < q[t]; ++i, ++rem[t]) {
+            csr_colind[rem[t]] = __ldg(colind + i);
+            csr_val[rem[t]] = val ? __ldg(val + i) : 1.0f;
+          }
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < R; ++t) {
+        if (head[t] == bmin) {
+          p[t] = q[t];
+          head[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) / bs : INT_MAX;
+        }
+      }
+    }
+    if (MODE == 0) {
+      if (lane == 0) bsr_counts[ib] = step;
+#pragma unroll
+      for (int t = 0; t < R; ++t) {
+        const int r = lane + 32 * t;
+        if (r < bs && ib * bs + r < m) csr_counts[ib * bs + r] = rem[t];
+      }
+    }
+  }
+}
+
+template <int MODE>
+int launch_divide(int dir, int m, int mb, int bs, int thr, const int* rowptr, const int* colind, const float* val,
+                  int* bsr_counts, int* csr_counts, const int* bsr_rowptr, int* bsr_colind, float* bsr_val,
+                  const int* csr_rowptr, int* csr_colind, float* csr_val, cudaStream_t st) {
+  const int R = (bs + 31) / 32;
+  int wpc = kWarpsPerCta;
+  size_t smem = 0;
+  if (MODE == 1) {
+    const size_t per_warp = sizeof(float) * (size_t)bs * bs;
+    while (wpc > 1 && per_warp * wpc > 200 * 1024) wpc >>= 1;
+    smem = per_warp * wpc;
+  }
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  const int64_t want = ((int64_t)mb + wpc - 1) / wpc;
+  const int grid = (int)(want < (int64_t)nsm * 16 ? (want > 0 ? want : 1) : (int64_t)nsm * 16);
+#define SPMMDB_LAUNCH_DIV(RR)                                                                                    \
+  do {                                                                                                           \
+    if (smem > 48 * 1024)                                                                                        \
+      SPMMDB_CUDA_OK(cudaFuncSetAttribute(divide_kernel<RR, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                          (int)smem));                                                           \
+    divide_kernel<RR, MODE><<<grid, kWarpsPerCta * 32, smem, st>>>(dir, m, mb, bs, thr, rowptr, colind, val,     \
+                                                                   bsr_counts, csr_counts, bsr_rowptr, bsr_colind, \
+                                                                   bsr_val, csr_rowptr, csr_colind, csr_val, wpc); \
+  } while (0)
+  if (R <= 1) SPMMDB_LAUNCH_DIV(1);
+  else if (R <= 2) SPMMDB_LAUNCH_DIV(2);
+  else SPMMDB_LAUNCH_DIV(4);
+#undef SPMMDB_LAUNCH_DIV
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
+int exclusive_scan(const int* counts, int n, int* sums, int* out, cudaStream_t st) {
+  const int ntiles = (n + kScanTile - 1) / kScanTile;
+  scan_tile_sums<<<ntiles, 256, 0, st>>>(counts, n, sums);
+  scan_sums_inplace<<<1, 256, 0, st>>>(sums, ntiles);
+  scan_apply<<<ntiles, 256, 0, st>>>(counts, n, sums, out);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
 template <int MODE>
 int launch_csr2bsr(int dir, int m, int mb, int bs, const int* rowptr, const int* colind, const float* val,
                    int* counts, const int* bsr_rowptr, int* bsr_colind, float* bsr_val, cudaStream_t st) {
@@ -321,4 +485,70 @@ extern "C" int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr
                                           csr_colind, csr_val);
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
+}
+
+// Smallest block count that the reference's test `float occupy = (count * 1.0) / bnum; occupy >= density`
+// (divide.cu:89-93) accepts; at least 1 (the reference would also emit EMPTY blocks for density <= 0).
+extern "C" int spmmdb_divide_threshold(int block_dim, float density) {
+  if (block_dim <= 0) return SPMMDB_ERR_INVALID_VALUE;
+  const int bnum = block_dim * block_dim;
+  auto ok = [&](int64_t c) { float occupy = (float)((c * 1.0) / bnum); return occupy >= density; };
+  if (!(density == density)) return INT_MAX;  // NaN: nothing passes
+  int64_t lo = 1, hi = INT_MAX;               // ok() is monotone in c
+  if (ok(lo)) return 1;
+  if (!ok(hi)) return INT_MAX;
+  while (hi - lo > 1) {
+    const int64_t mid = lo + (hi - lo) / 2;
+    if (ok(mid)) hi = mid; else lo = mid;
+  }
+  return (int)hi;
+}
+
+extern "C" int spmmdb_divide_nnz(int m, int n, const int* rowptr, const int* colind, int block_dim, float density,
+                                 int* bsr_rowptr, int* csr_rowptr, int* nnzb_host, int* csr_nnz_host, void* stream) {
+  if (m < 0 || n < 0 || block_dim <= 0 || block_dim > 128) return SPMMDB_ERR_INVALID_VALUE;
+  if (bsr_rowptr == nullptr || csr_rowptr == nullptr || nnzb_host == nullptr || csr_nnz_host == nullptr)
+    return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int mb = (m + block_dim - 1) / block_dim;
+  if (mb == 0) {
+    SPMMDB_CUDA_OK(cudaMemsetAsync(bsr_rowptr, 0, sizeof(int), st));
+    SPMMDB_CUDA_OK(cudaMemsetAsync(csr_rowptr, 0, sizeof(int), st));
+    SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+    *nnzb_host = 0; *csr_nnz_host = 0;
+    return SPMMDB_OK;
+  }
+  if (rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  const int ntiles = (m + kScanTile - 1) / kScanTile + 1;
+  int* ws = (int*)scratch(kScratchConvert, sizeof(int) * ((size_t)mb + (size_t)m + ntiles + 8), st);
+  if (ws == nullptr) return SPMMDB_ERR_ALLOC;
+  int* bsr_counts = ws;
+  int* csr_counts = ws + mb;
+  int* sums = ws + mb + m;
+  const int thr = spmmdb_divide_threshold(block_dim, density);
+  int rc = launch_divide<0>(SPMMDB_DIR_ROW, m, mb, block_dim, thr, rowptr, colind, nullptr, bsr_counts, csr_counts,
+                            nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st);
+  if (rc != SPMMDB_OK) return rc;
+  if ((rc = exclusive_scan(bsr_counts, mb, sums, bsr_rowptr, st)) != SPMMDB_OK) return rc;
+  if ((rc = exclusive_scan(csr_counts, m, sums, csr_rowptr, st)) != SPMMDB_OK) return rc;
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(nnzb_host, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(csr_nnz_host, csr_rowptr + m, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  return SPMMDB_OK;
+}
+
+extern "C" int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const int* colind, const float* val,
+                                 int block_dim, float density, const int* bsr_rowptr, int* bsr_colind,
+                                 float* bsr_val, const int* csr_rowptr, int* csr_colind, float* csr_val,
+                                 void* stream) {
+  if (m < 0 || n < 0 || block_dim <= 0 || block_dim > 128) return SPMMDB_ERR_INVALID_VALUE;
+  if (dir != SPMMDB_DIR_ROW && dir != SPMMDB_DIR_COLUMN) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  const int mb = (m + block_dim - 1) / block_dim;
+  if (mb == 0) return SPMMDB_OK;
+  if (rowptr == nullptr || bsr_rowptr == nullptr || csr_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  const int thr = spmmdb_divide_threshold(block_dim, density);
+  return launch_divide<1>(dir, m, mb, block_dim, thr, rowptr, colind, val, nullptr, nullptr, bsr_rowptr, bsr_colind,
+                          bsr_val, csr_rowptr, csr_colind, csr_val, (cudaStream_t)stream);
 }

@@ -36,15 +36,18 @@ struct CsrArgs {
   float alpha, beta;
   int seg;              // row segment length (power of two)
   // long-row queue (scratch)
-  int* counters;        // [0] = long rows, [1] = segments, [2] = overflow flag
+  int* counters;        // [0] = long rows, [1] = segments, [2] = overflow flag, [3] = work items taken,
+                        // [4] = segments taken (stream path)
   LongRow* long_rows;   // capacity cap_rows
   int* seg_owner;       // capacity cap_segs: segment -> long row slot
+  unsigned long long* seg_entry;  // stream path: (epoch << 32 | slot), published AFTER long_rows[slot]
   int* done;            // capacity cap_rows, zero between calls
   float* partial;       // capacity cap_segs * Kpad floats
   int cap_rows, cap_segs;
   int Kpad;             // K rounded up to 4
   int epoch;            // call counter: tells this call's queue entries from stale ones
   int rpi;              // stream kernel: rows per work item (<= 32)
+  int inline_segs;      // stream kernel: warps take queued segments between items (else: long-row kernel after)
 };
 
 template <typename V> struct VecOps;
@@ -73,8 +76,8 @@ template <> struct VecOps<float> {
 // lanes of the warp (shuffles); groups whose range is empty idle.
 // nvec = number of V-vectors per row of B that this column tile covers,
 // vbase = first vector index of the tile.
-template <typename V, int LPR, int VEC, int U>
-__device__ __forceinline__ void accumulate_segment(const CsrArgs& a, int lb, int hb, int sub, int grp,
+template <typename V, int LPR, int VEC, int U, typename Args>
+__device__ __forceinline__ void accumulate_segment(const Args& a, int lb, int hb, int sub, int grp,
                                                    int vbase, int nvec, V (&acc)[VEC]) {
   using Ops = VecOps<V>;
   const V* __restrict__ Bv = reinterpret_cast<const V*>(a.B);
@@ -121,8 +124,8 @@ __device__ __forceinline__ void accumulate_segment(const CsrArgs& a, int lb, int
   }
 }
 
-template <typename V, int LPR, int VEC>
-__device__ __forceinline__ void store_row(const CsrArgs& a, int row, int sub, int vbase, int nvec,
+template <typename V, int LPR, int VEC, typename Args>
+__device__ __forceinline__ void store_row(const Args& a, int row, int sub, int vbase, int nvec,
                                           const V (&acc)[VEC]) {
   using Ops = VecOps<V>;
   V* __restrict__ Cv = reinterpret_cast<V*>(a.C) + (int64_t)row * (a.ldc / Ops::W) + vbase + sub;
@@ -269,6 +272,39 @@ __global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
 
 
 // ---------------------------------------------------------------------------
+// Segment queue of the stream path.  Producers (any lane that meets a row longer than `seg`) take a
+// slot and a range of tickets, write the row record, fence, publish one 64-bit entry per ticket
+// (epoch << 32 | slot) and release that many units of a counting semaphore.  Consumers take a unit
+// of the semaphore (so the number of claims never passes the number of published tickets), then
+// the next ticket index, and wait for that entry if another producer is still between its
+// allocation and its publication (it publishes without waiting on anybody).  A CAS on the ticket
+// index instead of the semaphore serialised the whole GPU on one round trip per claim.  A row record that did not fit the
+// queue publishes void entries and is processed by its producer instead.
+__device__ __forceinline__ int publish_long_row(const CsrArgs& a, int row, int len) {
+  const int nseg = (len + a.seg - 1) / a.seg;
+  const int slot = atomicAdd(a.counters + 0, 1);
+  const int seg_base = atomicAdd(a.counters + 1, nseg);
+  const bool ok = slot < a.cap_rows && seg_base + nseg <= a.cap_segs;
+  if (ok) {
+    a.long_rows[slot] = LongRow{row, seg_base, nseg, a.epoch};
+    __threadfence();
+  } else {
+    atomicExch(a.counters + 2, 1);  // queue full (caller's nnz was too small): the row is done in place
+  }
+  if (!a.inline_segs) {
+    if (ok) for (int t = 0; t < nseg; ++t) a.seg_owner[seg_base + t] = slot;
+    return ok ? 1 : 0;
+  }
+  const unsigned long long ent = ((unsigned long long)(unsigned)a.epoch << 32) | (ok ? (unsigned)slot : 0xffffffffu);
+  int pub = 0;
+  for (int t = 0; t < nseg; ++t)
+    if (seg_base + t < a.cap_segs) { *(volatile unsigned long long*)(a.seg_entry + seg_base + t) = ent; ++pub; }
+  __threadfence();
+  atomicAdd(a.counters + 5, pub);  // semaphore: tickets that may be claimed
+  return ok ? 1 : 0;
+}
+
+// ---------------------------------------------------------------------------
 // Stream kernel (K % 4 == 0, K <= 512): persistent warps pull work items of
 // `rpi` consecutive rows from a global counter and walk the item's non-zero
 // stream [rowptr[r0], rowptr[r0 + rpi]) in coalesced chunks of 32 (col, val)
@@ -278,8 +314,18 @@ __global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
 // batch in CSR order and stores a row whenever the stream crosses its end.  All
 // control flow is warp-uniform (every lane handles the same non-zero, VEC
 // float4 columns of it), and each output element is still the sequential fp32
-// FMA chain of the reference kernel.  Rows longer than `seg` are skipped here
-// and queued for csrmm_long_kernel.
+// FMA chain of the reference kernel.
+//
+// Rows longer than `seg` are cut into row-relative segments and queued; a queued
+// segment is just a one-row work item whose output is a partial-sum row in
+// scratch, so the SAME loop body serves both.  Warps take queued segments before
+// the next item: a hub row is then gathered while the rows around it are being
+// streamed and its neighbourhood of B is in L2 (a separate launch afterwards
+// re-read it from DRAM: 9 GB per call on the products-shaped graph).  The warp
+// that finishes a row's last segment adds the partials in segment order, so the
+// result does not depend on who computed what.  The kernel is launched twice:
+// the second launch finds the item counter exhausted and only sweeps segments
+// queued after a warp's last look at the queue.
 template <int VEC, int U, int MINB>
 __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a) {
   using Ops = VecOps<float4>;
@@ -296,31 +342,57 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
   int item = 0;
   if (lane == 0) item = atomicAdd(a.counters + 3, 1);
   item = __shfl_sync(FULL, item, 0);
-  while (item < nitems) {
-    int next_item = 0;
-    if (lane == 0) next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the loop
-
-    const int r0 = item * a.rpi;
-    const int nrows = min(a.rpi, a.m - r0);
-    int s = 0, e = 0;
-    if (lane < nrows) {
-      s = __ldg(a.rowptr + r0 + lane);
-      e = __ldg(a.rowptr + r0 + lane + 1);
-    }
-    int lng = (e - s) > a.seg;
-    if (__any_sync(FULL, lng)) {
-      if (lng) {
-        const int nseg = (e - s + a.seg - 1) / a.seg;
-        const int slot = atomicAdd(a.counters + 0, 1);
-        const int seg_base = atomicAdd(a.counters + 1, nseg);
-        if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
-          atomicExch(a.counters + 2, 1);
-          lng = 0;  // queue full (caller's nnz was too small): do the row here
-        } else {
-          a.long_rows[slot] = LongRow{r0 + lane, seg_base, nseg, a.epoch};
-          for (int t = 0; t < nseg; ++t) a.seg_owner[seg_base + t] = slot;
-        }
+  int pending = a.inline_segs;  // look at the queue before the first item: the second launch has only the queue left
+  for (;;) {
+    // ---- pick work: a queued segment if there is one, else the item already claimed
+    int t = -1;
+    if (pending) {
+      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
+        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
+        else atomicAdd(a.counters + 5, 1);
       }
+      t = __shfl_sync(FULL, t, 0);
+    }
+    pending = 0;
+    int next_item = item;
+    int nrows = 1, s = 0, e = 0, lng = 0;
+    float4* __restrict__ obase;  // output row 0 of this work unit (this lane's first column)
+    int ldo;
+    if (t >= 0) {
+      volatile unsigned long long* pe = a.seg_entry + t;
+      unsigned long long ent;
+      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
+      __threadfence();
+      pending = 1;  // keep draining the queue
+      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket (its row did not fit the queue)
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));  // written during this kernel
+      if (lane == 0) {
+        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
+        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
+      }
+      // partial sums are stored raw; alpha / beta are applied by the final add
+      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * (a.Kpad >> 2) + lane;
+      ldo = 0;
+    } else {
+      if (item >= nitems) break;
+      if (lane == 0) {
+        next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the loop
+        // queue look, also consumed at the bottom (a little stale is fine: the second launch sweeps up)
+        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
+      }
+      const int r0 = item * a.rpi;
+      nrows = min(a.rpi, a.m - r0);
+      if (lane < nrows) {
+        s = __ldg(a.rowptr + r0 + lane);
+        e = __ldg(a.rowptr + r0 + lane + 1);
+      }
+      lng = (e - s) > a.seg;
+      if (__any_sync(FULL, lng)) {
+        pending = a.inline_segs;
+        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
+      }
+      ldo = (int)(a.ldc >> 2);
+      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo + lane;
     }
     const int S = __shfl_sync(FULL, s, 0);
     const int E = __shfl_sync(FULL, e, nrows - 1);
@@ -335,12 +407,13 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
 
     auto flush_advance = [&]() {
       if (!cl) {
-        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)(r0 + cr) * (a.ldc >> 2) + lane;
+        float4* __restrict__ Cv = obase + (int64_t)cr * ldo;
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
           if (colok[i]) {
             float4 out;
-            if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[32 * i]);
+            if (t >= 0) out = acc[i];
+            else if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[32 * i]);
             else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i]);
             else out = acc[i];
             __stcs(Cv + 32 * i, out);
@@ -432,7 +505,33 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
     }
     while (cr < nrows) flush_advance();  // last row and trailing empty rows
 
-    item = __shfl_sync(FULL, next_item, 0);
+    if (t >= 0) {
+      // publish the partial; the warp that finishes the row's last segment adds them in segment order
+      __threadfence();
+      __syncwarp();
+      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
+      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
+      int last = 0;
+      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
+      last = __shfl_sync(FULL, last, 0);
+      if (last) {
+        __threadfence();
+        if (lane == 0) a.done[seg_slot] = 0;
+        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * (a.Kpad >> 2) + lane;
+        for (int q = 0; q < seg_nseg; ++q, p += (a.Kpad >> 2)) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i)
+            if (colok[i]) {
+              if (q == 0) acc[i] = __ldcg(p + 32 * i); else Ops::add(acc[i], __ldcg(p + 32 * i));
+            }
+        }
+        store_row<float4, 32, VEC>(a, r0, lane, 0, nvec, acc);
+      }
+    } else {
+      item = __shfl_sync(FULL, next_item, 0);
+    }
+    pending = __shfl_sync(FULL, pending, 0);
   }
 }
 
@@ -611,7 +710,8 @@ template <int VEC, int U, int MINB>
 int launch_stream(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
   csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  csrmm_long_kernel<float4, 32, VEC, (VEC >= 3 ? 4 : 8)><<<long_ctas, 256, 0, st>>>(a);
+  if (a.inline_segs) csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
+  else csrmm_long_kernel<float4, 32, VEC, (VEC >= 3 ? 4 : 8)><<<long_ctas, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
 }
@@ -650,6 +750,9 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
   a.seg = spmmdb_csrmm_segment(nnz);
+  // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
+  // ~10 dependent L2 round trips, the grid-stride long-row kernel half of that (0.155 vs 0.194 ms on C2).
+  a.inline_segs = a.seg >= 256;
   a.Kpad = (K + 3) & ~3;
   static int g_epoch = 0;
   a.epoch = ++g_epoch;
@@ -659,7 +762,8 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.cap_rows = (int)max_long;
   a.cap_segs = (int)max_segs;
   const size_t hdr = 64;
-  const size_t bytes_q = hdr + sizeof(LongRow) * max_long + sizeof(int) * max_segs + sizeof(int) * max_long;
+  const size_t bytes_q = hdr + sizeof(LongRow) * max_long + sizeof(int) * max_segs + sizeof(int) * max_long + 16 +
+                         sizeof(unsigned long long) * max_segs;
   char* q = (char*)scratch(kScratchCsrLong, bytes_q, st);
   float* part = (float*)scratch(kScratchCsrPartial, sizeof(float) * (size_t)max_segs * a.Kpad, st);
   if (q == nullptr || part == nullptr) return SPMMDB_ERR_ALLOC;
@@ -667,6 +771,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.long_rows = (LongRow*)(q + hdr);
   a.seg_owner = (int*)(q + hdr + sizeof(LongRow) * max_long);
   a.done = a.seg_owner + max_segs;
+  a.seg_entry = (unsigned long long*)(((uintptr_t)(a.done + max_long) + 15) & ~(uintptr_t)15);
   a.partial = part;
   SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
@@ -720,7 +825,9 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
 }  // namespace spmmdb
 
 extern "C" int spmmdb_csrmm_segment(int64_t nnz) {
+  static const int seg_env = [] { const char* e = getenv("SPMMDB_CSR_SEG"); return e ? atoi(e) : 0; }();
+  if (seg_env >= 32 && (seg_env & (seg_env - 1)) == 0) return seg_env;  // tuning knob (power of two)
   if (nnz < (int64_t)4 << 20) return 64;
   if (nnz < (int64_t)32 << 20) return 256;
-  return 1024;
+  return 512;  // B200 sweep on the products-shaped graph: 256 / 512 / 1024 / 2048 -> 4.75 / 4.74 / 4.97 / 5.21 ms
 }

@@ -123,3 +123,30 @@ def bsr2csr(mb, nb, bsr_rowptr, bsr_colind, bsr_val, block_dim, direction=DIR_RO
                                   _p(csr_rowptr), _p(csr_colind), _p(csr_val), _stream())
     check(rc, "spmmdb_bsr2csr_f32")
     return csr_rowptr, csr_colind, csr_val
+
+
+def divide_threshold(block_dim, density):
+    return lib().spmmdb_divide_threshold(block_dim, density)
+
+
+def divide(m, n, rowptr, colind, val, block_dim, density, direction=DIR_ROW):
+    """divide_matrix (divide.cu:52-127) on the device: blocks with fill >= density -> BSR, the rest ->
+    remainder CSR.  Returns (csr_rowptr, csr_colind, csr_val, bsr_rowptr, bsr_colind, bsr_val)."""
+    _dev(rowptr, colind, val)
+    dev = rowptr.device
+    mb = (m + block_dim - 1) // block_dim
+    bsr_rowptr = torch.empty(mb + 1, dtype=torch.int32, device=dev)
+    csr_rowptr = torch.empty(m + 1, dtype=torch.int32, device=dev)
+    nnzb, cnnz = C.c_int(0), C.c_int(0)
+    rc = lib().spmmdb_divide_nnz(m, n, _p(rowptr), _p(colind), block_dim, density, _p(bsr_rowptr), _p(csr_rowptr),
+                                 C.byref(nnzb), C.byref(cnnz), _stream())
+    check(rc, "spmmdb_divide_nnz")
+    bsr_colind = torch.empty(nnzb.value, dtype=torch.int32, device=dev)
+    bsr_val = torch.empty(nnzb.value * block_dim * block_dim, dtype=torch.float32, device=dev)
+    csr_colind = torch.empty(cnnz.value, dtype=torch.int32, device=dev)
+    csr_val = torch.empty(cnnz.value, dtype=torch.float32, device=dev)
+    rc = lib().spmmdb_divide_f32(direction, m, n, _p(rowptr), _p(colind), _p(val), block_dim, density,
+                                 _p(bsr_rowptr), _p(bsr_colind), _p(bsr_val), _p(csr_rowptr), _p(csr_colind),
+                                 _p(csr_val), _stream())
+    check(rc, "spmmdb_divide_f32")
+    return csr_rowptr, csr_colind, csr_val, bsr_rowptr, bsr_colind, bsr_val
