@@ -184,23 +184,28 @@ def calculate_nnzb(rowptr, colind, bs):
     return int(f(rowptr.size - 1, rowptr, colind, bs))
 
 
-def divide_matrix(rowptr, colind, bs, density):
-    """divide.cu:52-127 -> (csr_rowptr, csr_colind, bsr_rowptr, bsr_colind, bsr_val)."""
+def divide_matrix(rowptr, colind, bs, density, val=None):
+    """divide.cu:52-127 -> (csr_rowptr, csr_colind, bsr_rowptr, bsr_colind, bsr_val); with val (the
+    reference uses unit weights) also csr_val as a sixth item."""
     rowptr, colind = _i32(rowptr), _i32(colind)
     n = rowptr.size - 1
     nb = (n + bs - 1) // bs
     f = lib().oracle_divide_matrix
-    f.argtypes = [C.c_int, _i32p, _i32p, C.c_int, C.c_float] + [C.c_void_p] * 5 + [C.POINTER(C.c_int64)]
+    f.argtypes = [C.c_int, _i32p, _i32p, C.c_void_p, C.c_int, C.c_float] + [C.c_void_p] * 6 + [C.POINTER(C.c_int64)]
+    v = None if val is None else _f32(val)
+    vptr = None if v is None else v.ctypes.data
     cnnz = C.c_int64(0)
-    nnzb = int(f(n, rowptr, colind, bs, density, None, None, None, None, None, C.byref(cnnz)))
+    nnzb = int(f(n, rowptr, colind, vptr, bs, density, None, None, None, None, None, None, C.byref(cnnz)))
     crp = np.zeros(n + 1, np.int32)
     cci = np.zeros(max(cnnz.value, 1), np.int32)
+    cv = np.zeros(max(cnnz.value, 1), np.float32)
     brp = np.zeros(nb + 1, np.int32)
     bci = np.zeros(max(nnzb, 1), np.int32)
     bv = np.zeros(max(nnzb, 1) * bs * bs, np.float32)
-    f(n, rowptr, colind, bs, density, crp.ctypes.data, cci.ctypes.data, brp.ctypes.data,
+    f(n, rowptr, colind, vptr, bs, density, crp.ctypes.data, cci.ctypes.data, cv.ctypes.data, brp.ctypes.data,
       bci.ctypes.data, bv.ctypes.data, C.byref(cnnz))
-    return crp, cci[:cnnz.value], brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs)
+    out = (crp, cci[:cnnz.value], brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs))
+    return out if val is None else out + (cv[:cnnz.value],)
 
 
 # --------------------------------------------------------------------------
@@ -275,3 +280,37 @@ def ref_rcmk_graph(rowptr, colind):
     L.ref_rcmk_graph.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p]
     L.ref_rcmk_graph(n, rowptr, colind, nrp, nci)
     return nrp, nci[:colind.size]
+
+
+_ref_divide = None
+
+
+def ref_divide_lib():
+    global _ref_divide
+    p = os.path.join(HERE, "_ref", "libref_divide.so")
+    if _ref_divide is None and os.path.exists(p):
+        try:
+            _ref_divide = C.CDLL(p)
+        except OSError:
+            return None
+    return _ref_divide
+
+
+def ref_divide_matrix(rowptr, colind, bs, density):
+    """The reference's own divide_matrix (divide.cu:52-127): unit weights."""
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    nb = (n + bs - 1) // bs
+    f = ref_divide_lib().ref_divide_matrix
+    f.restype = C.c_longlong
+    f.argtypes = [C.c_int, _i32p, _i32p, C.c_int, C.c_float] + [C.c_void_p] * 5 + [C.POINTER(C.c_longlong)]
+    cnnz = C.c_longlong(0)
+    nnzb = int(f(n, rowptr, colind, bs, density, None, None, None, None, None, C.byref(cnnz)))
+    crp = np.zeros(n + 1, np.int32)
+    cci = np.zeros(max(cnnz.value, 1), np.int32)
+    brp = np.zeros(nb + 1, np.int32)
+    bci = np.zeros(max(nnzb, 1), np.int32)
+    bv = np.zeros(max(nnzb, 1) * bs * bs, np.float32)
+    f(n, rowptr, colind, bs, density, crp.ctypes.data, cci.ctypes.data, brp.ctypes.data, bci.ctypes.data,
+      bv.ctypes.data, C.byref(cnnz))
+    return crp, cci[:cnnz.value], brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs)

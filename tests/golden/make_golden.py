@@ -84,6 +84,29 @@ def main():
     np.savez_compressed(os.path.join(HERE, "ref_text_formats.npz"), rowptr=rp4, colind=ci4,
                         indptr_txt=np.array(indptr_txt), indices_txt=np.array(indices_txt),
                         edge_txt=np.array(edge_txt), g_rowptr=grp[:n + 1], g_colind=gci[:nnz.value])
+
+    # 5. divide_matrix (divide.cu:52-127): hybrid dense-block split on a graph with planted dense
+    #    diagonal blocks (ragged last block row: 205 rows, bs 8 / 16 / 3), several densities
+    assert O.ref_divide_lib() is not None, "oracle/_ref/libref_divide.so not built"
+    n5 = 205
+    rows = []
+    for i in range(n5):
+        c = set(rng.choice(n5, size=int(rng.poisson(4)), replace=False).tolist())
+        if (i // 16) % 2 == 0:  # every other 16-row band has a dense diagonal block
+            lo = (i // 16) * 16
+            c |= set(j for j in range(lo, min(lo + 16, n5)) if rng.uniform() < 0.7)
+        rows.append(np.array(sorted(c), np.int32))
+    rp5 = np.zeros(n5 + 1, np.int32)
+    rp5[1:] = np.cumsum([len(r) for r in rows])
+    ci5 = np.concatenate(rows).astype(np.int32)
+    out = dict(rowptr=rp5, colind=ci5)
+    cases = [(8, 0.5), (16, 0.25), (16, 0.6), (3, 0.34), (16, 1.0), (32, 0.05)]
+    out["cases"] = np.array(cases, np.float64)
+    for k, (bs, dens) in enumerate(cases):
+        crp, cci, brp, bci, bv = O.ref_divide_matrix(rp5, ci5, bs, dens)
+        out.update({f"c{k}_csr_rowptr": crp, f"c{k}_csr_colind": cci, f"c{k}_bsr_rowptr": brp,
+                    f"c{k}_bsr_colind": bci, f"c{k}_bsr_val": bv})
+    np.savez_compressed(os.path.join(HERE, "ref_divide.npz"), **out)
     print("golden fixtures written to", HERE)
 
 

@@ -42,7 +42,7 @@ def test_binding_covers_header(L):
 
 def test_version_and_status(L):
     assert b"spmmdb" in L.spmmdb_version()
-    assert L.spmmdb_csrmm_segment(1000) == 64 and L.spmmdb_csrmm_segment(62_000_000) == 1024
+    assert L.spmmdb_csrmm_segment(1000) == 64 and L.spmmdb_csrmm_segment(62_000_000) == 512
 
 
 def test_validation_without_device(L):

@@ -9,7 +9,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "drivers", "bin")
-PROGS = ["run_csrmm", "run_bsrmm", "test_csrmm", "test_bsrmm", "check_result", "csr2bsr", "bsr2csr", "block_cublas"]
+PROGS = ["run_csrmm", "run_bsrmm", "test_csrmm", "test_bsrmm", "check_result", "csr2bsr", "bsr2csr", "block_cublas", "divide"]
 
 
 def _build():
@@ -124,3 +124,44 @@ def test_microbench_drivers_print_reference_lines(tmp_path):
         assert abs(sums[0] - sums[1]) <= 1e-3 * max(1.0, abs(sums[1]))
     rc, out = _run([os.path.join(BIN, "test_block_cublas"), "0.0005", "16", "64"], str(tmp_path))
     assert rc == 0 and "block gemm cost time" in out, out
+
+
+@pytest.mark.gpu
+def test_divide_cli_and_agreement(tmp_path):
+    """divide <graph> <bsize> <dim> <rocsparse|cusparse> <transB> <density> (divide.cu:205-391): printed lines
+    kept, hybrid product == plain CSR product, our BSR part == the vendor cusparseSbsrmm on the same split."""
+    _build()
+    os.makedirs(tmp_path / "tmp")
+    rng = np.random.default_rng(21)
+    n, band = 2000, 16
+    rows = []
+    for i in range(n):
+        c = set(rng.choice(n, size=int(rng.poisson(5)), replace=False).tolist())
+        if (i // band) % 2 == 0:
+            lo = (i // band) * band
+            c |= set(j for j in range(lo, min(lo + band, n)) if rng.uniform() < 0.7)
+        rows.append(sorted(c))
+    rp = np.concatenate([[0], np.cumsum([len(r) for r in rows])])
+    ci = np.concatenate([np.asarray(r, np.int64) for r in rows])
+    with open(tmp_path / "tmp" / "band_indptr.txt", "w") as f:
+        f.write(f"{rp.size}\n" + " ".join(map(str, rp.tolist())))
+    with open(tmp_path / "tmp" / "band_indices.txt", "w") as f:
+        f.write(f"{ci.size}\n" + " ".join(map(str, ci.tolist())))
+    sums = {}
+    for impl, math, tb in (("cusparse", "fp32", 1), ("rocsparse", "fp32", 1), ("rocsparse", "tf32", 1),
+                           ("rocsparse", "fp32", 0), ("cusparse", "fp32", 0)):
+        rc, out = _run([os.path.join(BIN, "divide"), "band", "16", "64", impl, str(tb), "0.4"], str(tmp_path),
+                       {"SPMMDB_BSRMM_MATH": math})
+        assert rc == 0, out
+        m = re.search(r"csr nnz = (\d+)    bsr nnzb = (\d+)", out)
+        assert m and int(m.group(1)) < ci.size and int(m.group(2)) > 0, out
+        for line in ("tmp/band", "csr to adj...", "divide matrix...", "prepare y and z...", "end"):
+            assert line in out, out
+        assert re.search(r"csrmm cost time:  \d+\.\d{10} ms", out) and re.search(r"bsrmm cost time:  \d+\.\d{10} ms", out)
+        assert re.search(r"total cost time:  \d+\.\d{10} ms", out) and re.search(r"\d+\.\d{5}\+\d+\.\d{5}=\d+\.\d{5}", out)
+        diff = float(re.search(r"max \|hybrid - csr\| = (\S+),", out).group(1))
+        assert diff <= (2e-2 if math == "tf32" else 1e-4), out
+        sums[(impl, math, tb)] = float(re.search(r"checksum (\S+)", out).group(1))
+    for tb in (0, 1):
+        ref = sums[("cusparse", "fp32", tb)]
+        assert abs(sums[("rocsparse", "fp32", tb)] - ref) <= 1e-3 * max(1.0, abs(ref))

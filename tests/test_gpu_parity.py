@@ -330,3 +330,110 @@ def test_check_result_harness(pkg, oracle):
     assert float((z1 - z2).abs().max()) < 1e-4
     ref = oracle.csrmm(rp, ci, v, y, dim)
     assert np.max(np.abs(z1.cpu().numpy().T - ref)) < 1e-4
+
+
+# ----------------------------------------------------------------------------- divide (hybrid split)
+def _banded_graph(rng, n, band=16, p_dense=0.7, avg=4):
+    rows = []
+    for i in range(n):
+        c = set(rng.choice(n, size=min(int(rng.poisson(avg)), n), replace=False).tolist())
+        if (i // band) % 2 == 0:
+            lo = (i // band) * band
+            c |= set(j for j in range(lo, min(lo + band, n)) if rng.uniform() < p_dense)
+        rows.append(np.array(sorted(c), np.int32))
+    rp = np.zeros(n + 1, np.int32)
+    rp[1:] = np.cumsum([len(r) for r in rows])
+    ci = np.concatenate(rows).astype(np.int32) if rp[-1] else np.zeros(0, np.int32)
+    return rp, ci
+
+
+def test_divide_golden_reference(pkg, golden_dir):
+    """GPU divide against the outputs of the reference's own divide_matrix (unit weights, val = NULL)."""
+    import os
+    d = np.load(os.path.join(golden_dir, "ref_divide.npz"))
+    rp, ci = d["rowptr"], d["colind"]
+    n = rp.size - 1
+    for k, (bs, dens) in enumerate(d["cases"]):
+        bs = int(bs)
+        crp, cci, cv, brp, bci, bv = pkg.divide(n, n, dev(rp), dev(ci), None, bs, float(dens))
+        assert np.array_equal(crp.cpu().numpy(), d[f"c{k}_csr_rowptr"])
+        assert np.array_equal(cci.cpu().numpy(), d[f"c{k}_csr_colind"])
+        assert np.array_equal(brp.cpu().numpy(), d[f"c{k}_bsr_rowptr"])
+        assert np.array_equal(bci.cpu().numpy(), d[f"c{k}_bsr_colind"])
+        assert np.array_equal(bv.cpu().numpy(), d[f"c{k}_bsr_val"].ravel())
+        assert np.all(cv.cpu().numpy() == 1.0)
+
+
+@pytest.mark.parametrize("bs,dens", [(2, 0.6), (5, 0.3), (16, 0.25), (16, 0.6), (32, 0.1), (33, 0.05), (64, 0.02),
+                                     (16, 0.0), (16, 1.5)])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_divide_bit_exact_with_values(pkg, oracle, bs, dens, direction):
+    rng = np.random.default_rng(bs * 7 + direction)
+    n = 1000 + bs // 2  # ragged last block row
+    rp, ci = _banded_graph(rng, n, band=max(bs, 4))
+    v = rng.uniform(-1, 1, ci.size).astype(np.float32)
+    crp, cci, cv, brp, bci, bv = pkg.divide(n, n, dev(rp), dev(ci), dev(v), bs, dens, direction=direction)
+    # density <= 0: the reference would emit every (also empty) block; the product emits the non-empty ones
+    o_dens = dens if dens > 0 else 1e-9
+    ocrp, occi, obrp, obci, obv, ocv = oracle.divide_matrix(rp, ci, bs, o_dens, val=v)
+    if direction == 1:
+        obv = obv.transpose(0, 2, 1)
+    assert np.array_equal(crp.cpu().numpy(), ocrp) and np.array_equal(cci.cpu().numpy(), occi)
+    assert np.array_equal(cv.cpu().numpy(), ocv)
+    assert np.array_equal(brp.cpu().numpy(), obrp) and np.array_equal(bci.cpu().numpy(), obci)
+    assert np.array_equal(bv.cpu().numpy(), np.ascontiguousarray(obv).ravel())
+    if dens <= 0:
+        assert cci.numel() == 0      # everything is a block: plain csr2bsr
+    if dens > 1:
+        assert bci.numel() == 0      # nothing qualifies: the remainder is the input
+        assert np.array_equal(cci.cpu().numpy(), ci)
+
+
+def test_divide_empty_and_edge_inputs(pkg):
+    z = torch.zeros(1, dtype=torch.int32, device="cuda")
+    crp, cci, cv, brp, bci, bv = pkg.divide(0, 0, z, None, None, 16, 0.5)
+    assert crp.cpu().tolist() == [0] and brp.cpu().tolist() == [0] and cci.numel() == 0 and bci.numel() == 0
+    rp = torch.zeros(41, dtype=torch.int32, device="cuda")  # 40 empty rows
+    crp, cci, cv, brp, bci, bv = pkg.divide(40, 40, rp, None, None, 16, 0.5)
+    assert crp.cpu().tolist() == [0] * 41 and brp.cpu().tolist() == [0] * 4
+
+
+@pytest.mark.parametrize("math,tol", [(0, TOL_FP32), (1, TOL_TC), (2, TOL_TC)])
+def test_divide_hybrid_spmm_matches_csr(pkg, oracle, math, tol):
+    """divide.cu:348-373: C = A_csr * B (beta = 1 on zeroed C), then C += A_bsr * B; the sum is A * B."""
+    rng = np.random.default_rng(11)
+    bs, K = 16, 128
+    n = 64 * bs
+    rp, ci = _banded_graph(rng, n, band=bs, p_dense=0.8, avg=6)
+    v = rng.uniform(-1, 1, ci.size).astype(np.float32)
+    B = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    crp, cci, cv, brp, bci, bv = pkg.divide(n, n, dev(rp), dev(ci), dev(v), bs, 0.3)
+    assert 0 < bci.numel() and 0 < cci.numel() < ci.size
+    Bd = dev(B)
+    C = torch.zeros(n, K, device="cuda")
+    pkg.csrmm(crp, cci, cv, Bd, C, n, n, K, alpha=1.0, beta=1.0)
+    mb = n // bs
+    pkg.bsrmm(pkg.DIR_ROW, 1, mb, K, mb, bci.numel(), 1.0, bv, brp, bci, bs, Bd, K, 1.0, C, K,
+              c_layout=pkg.ROW_MAJOR, math=math)
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K) <= tol
+
+
+def test_divide_full_size_proteins_property(pkg):
+    """Size-independent property at the C3 (proteins-shaped) size: the two parts partition the non-zeros
+    (counts add up, every block meets the threshold, no remainder entry lies in a dense block)."""
+    from spmm_denseblock_b200 import graphs
+    rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=0.25)
+    n, nnz, bs, dens = rp.numel() - 1, ci.numel(), 16, 0.2
+    crp, cci, cv, brp, bci, bv = pkg.divide(n, n, rp, ci, None, bs, dens)
+    per_block = (bv.view(-1, bs * bs) != 0).sum(1)
+    assert int(per_block.sum()) + cci.numel() == nnz
+    assert int(per_block.min()) >= pkg.divide_threshold(bs, dens)
+    # remainder entries never fall in a dense block of their block row
+    mb = (n + bs - 1) // bs
+    deg = (crp[1:] - crp[:-1]).long()
+    rows = torch.arange(n, device="cuda").repeat_interleave(deg)
+    rem_key = (rows // bs) * mb + (cci.long() // bs)
+    bdeg = (brp[1:] - brp[:-1]).long()
+    blk_key = torch.arange(mb, device="cuda").repeat_interleave(bdeg) * mb + bci.long()
+    assert not torch.isin(rem_key, blk_key).any()

@@ -150,3 +150,33 @@ def test_permutate_properties(oracle):
     inv = np.argsort(perm).astype(np.int32)
     brp, bci = oracle.permutate_csr(prp, pci, inv)
     assert np.array_equal(brp, rp) and np.array_equal(bci, ci)
+
+
+def test_golden_ref_divide_matrix(oracle, golden_dir):
+    """oracle.divide_matrix against outputs of the reference's OWN divide_matrix (divide.cu:52-127, compiled
+    from /root/reference into oracle/_ref by oracle/Makefile; fixture made by tests/golden/make_golden.py)."""
+    d = np.load(os.path.join(golden_dir, "ref_divide.npz"))
+    for k, (bs, dens) in enumerate(d["cases"]):
+        crp, cci, brp, bci, bv = oracle.divide_matrix(d["rowptr"], d["colind"], int(bs), float(dens))
+        assert np.array_equal(crp, d[f"c{k}_csr_rowptr"]) and np.array_equal(cci, d[f"c{k}_csr_colind"])
+        assert np.array_equal(brp, d[f"c{k}_bsr_rowptr"]) and np.array_equal(bci, d[f"c{k}_bsr_colind"])
+        assert np.array_equal(bv, d[f"c{k}_bsr_val"])
+        # every non-zero lands in exactly one part
+        assert cci.size + int(np.count_nonzero(bv)) == d["colind"].size
+        if oracle.ref_divide_lib() is not None:  # live, when oracle/_ref is present
+            live = oracle.ref_divide_matrix(d["rowptr"], d["colind"], int(bs), float(dens))
+            for a, b in zip(live, (crp, cci, brp, bci, bv)):
+                assert np.array_equal(a, b)
+
+
+def test_divide_threshold_matches_reference_expression():
+    """spmmdb_divide_threshold (host function of the product library, no CUDA) = the smallest count the
+    reference's `float occupy = (count * 1.0) / bnum; occupy >= density` accepts (divide.cu:89-93)."""
+    import spmm_denseblock_b200 as pkg
+    rng = np.random.default_rng(5)
+    for bs in (2, 3, 8, 16, 32, 64):
+        for dens in [0.6, 0.1, 0.5, 1.0, 0.999, 1e-4, 0.3333333] + rng.uniform(0, 1, 20).tolist():
+            dens = float(np.float32(dens))
+            thr = pkg.divide_threshold(bs, dens)
+            ok = lambda c: np.float32((c * 1.0) / (bs * bs)) >= np.float32(dens)  # noqa: E731
+            assert ok(thr) and thr >= 1 and (thr == 1 or not ok(thr - 1)), (bs, dens, thr)
