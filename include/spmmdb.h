@@ -66,7 +66,7 @@ int spmmdb_device_sm(void);                   /* e.g. 100 on B200; <0 = no devic
  *   b_layout / c_layout  SPMMDB_ROW_MAJOR (ld >= K) or SPMMDB_COL_MAJOR
  *   With row-major B/C, alpha == 1, beta == 0 each output element is the fp32
  *   FMA chain in CSR order, i.e. bit-identical to the reference kernel, for
- *   every row of at most spmmdb_csrmm_segment(nnz) non-zeros; longer rows are
+ *   every row of at most spmmdb_csrmm_segment_for(m, nnz) non-zeros; longer rows are
  *   summed per fixed-size segment and the segment sums added in order
  *   (deterministic, independent of how rows are sharded over GPUs).
  * ------------------------------------------------------------------------ */
@@ -74,8 +74,18 @@ int spmmdb_csrmm_f32(int m, int k, int K, int64_t nnz, const int* rowptr, const 
                      const float* val, const float* B, int64_t ldb, int b_layout, float* C,
                      int64_t ldc, int c_layout, float alpha, float beta, void* stream);
 
-/* Row-segment length used for a matrix with `nnz` non-zeros (see above). */
+/* Row-segment length: rows of at most this many non-zeros are one sequential FMA chain.
+ *   spmmdb_csrmm_segment(nnz)         lower bound that depends on nnz alone (64 / 256 / 512)
+ *   spmmdb_csrmm_segment_for(m, nnz)  the length a call with these sizes uses: the above, raised to
+ *                                     the power of two >= 4 * average row length
+ *   spmmdb_set_csrmm_segment(seg)     process-wide override (power of two >= 32; 0 = automatic).  A row-
+ *                                     sharded run sets spmmdb_csrmm_segment_for(m, nnz) of the WHOLE matrix
+ *                                     on every rank, so that a row is cut the same way on any shard and
+ *                                     the concatenated shards equal the single-GPU result bit for bit. */
 int spmmdb_csrmm_segment(int64_t nnz);
+int spmmdb_csrmm_segment_for(int m, int64_t nnz);
+int spmmdb_set_csrmm_segment(int seg);  /* SPMMDB_OK or SPMMDB_ERR_INVALID_VALUE */
+int spmmdb_get_csrmm_segment(void);     /* the override, 0 = automatic */
 
 /* --------------------------------------------------------------------------
  * BSR x dense:  C = alpha * A_bsr * op(B) + beta * C
@@ -175,7 +185,8 @@ int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr,
  *   bounds    HOST out, parts + 1 entries: range g = [bounds[g], bounds[g+1]);
  *             boundary g = first row r with rowptr[r] >= g*nnz/parts, rounded down to `align`
  * Output rows are disjoint, so the sharded SpMM needs no reduction; the long-row
- * split of spmmdb_csrmm_f32 depends only on the row, so concatenated shards are
+ * split of spmmdb_csrmm_f32 depends only on the row and the segment length, so with
+ * the same spmmdb_set_csrmm_segment() on every rank concatenated shards are
  * bit-identical to the single-GPU result.
  * ------------------------------------------------------------------------ */
 int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds);

@@ -21,6 +21,9 @@ SIGNATURES = {
     "spmmdb_csrmm_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, c_i64, C.c_int, vp, c_i64, C.c_int,
                          C.c_float, C.c_float, vp],
     "spmmdb_csrmm_segment": [c_i64],
+    "spmmdb_csrmm_segment_for": [C.c_int, c_i64],
+    "spmmdb_set_csrmm_segment": [C.c_int],
+    "spmmdb_get_csrmm_segment": [],
     "spmmdb_bsrmm_f32": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_i64, C.c_int, C.c_float, vp, vp, vp, vp,
                          c_i64, C.c_float, vp, c_i64, C.c_int, C.c_int, vp],
     "spmmdb_block_gemm_f32": [C.c_int, C.c_int, c_i64, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp],

@@ -24,7 +24,7 @@ void set_last_error(const char* what, cudaError_t err, const char* file, int lin
 // never visible to the caller.  Allocation happens on first use / growth only
 // (cudaMalloc synchronises, steady-state calls stay asynchronous).  Newly
 // allocated memory is zero-filled.
-enum ScratchSlot { kScratchCsrLong = 0, kScratchCsrPartial, kScratchLayoutB, kScratchLayoutC,
+enum ScratchSlot { kScratchCsrLong = 0, kScratchCsrPartial, kScratchCsrDone, kScratchCsrEntry, kScratchLayoutB, kScratchLayoutC,
                    kScratchConvert, kScratchBsr, kScratchBsrA, kScratchBsrB, kScratchHostA, kScratchHostB, kScratchHostC,
                    kScratchSlots };
 void* scratch(int slot, size_t bytes, cudaStream_t stream);

@@ -749,7 +749,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   CsrArgs a;
   a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
-  a.seg = spmmdb_csrmm_segment(nnz);
+  a.seg = spmmdb_get_csrmm_segment() ? spmmdb_get_csrmm_segment() : spmmdb_csrmm_segment_for(m, nnz);
   // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
   // ~10 dependent L2 round trips, the grid-stride long-row kernel half of that (0.155 vs 0.194 ms on C2).
   a.inline_segs = a.seg >= 256;
@@ -762,16 +762,22 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.cap_rows = (int)max_long;
   a.cap_segs = (int)max_segs;
   const size_t hdr = 64;
-  const size_t bytes_q = hdr + sizeof(LongRow) * max_long + sizeof(int) * max_segs + sizeof(int) * max_long + 16 +
-                         sizeof(unsigned long long) * max_segs;
+  const size_t bytes_q = hdr + sizeof(LongRow) * max_long + sizeof(int) * max_segs;
   char* q = (char*)scratch(kScratchCsrLong, bytes_q, st);
   float* part = (float*)scratch(kScratchCsrPartial, sizeof(float) * (size_t)max_segs * a.Kpad, st);
-  if (q == nullptr || part == nullptr) return SPMMDB_ERR_ALLOC;
+  // `done` and `seg_entry` live in buffers of their own: the layout of the queue buffer moves with nnz, and
+  // both are read before this call writes them -- `done` must be all zero (the last finisher of a row restores
+  // it), a `seg_entry` must never carry this call's epoch before its producer published it.  In a shared buffer
+  // a later call with another nnz found an earlier call's row records under them.
+  int* done = (int*)scratch(kScratchCsrDone, sizeof(int) * (size_t)max_long, st);
+  unsigned long long* entry =
+      (unsigned long long*)scratch(kScratchCsrEntry, sizeof(unsigned long long) * (size_t)max_segs, st);
+  if (q == nullptr || part == nullptr || done == nullptr || entry == nullptr) return SPMMDB_ERR_ALLOC;
   a.counters = (int*)q;
   a.long_rows = (LongRow*)(q + hdr);
   a.seg_owner = (int*)(q + hdr + sizeof(LongRow) * max_long);
-  a.done = a.seg_owner + max_segs;
-  a.seg_entry = (unsigned long long*)(((uintptr_t)(a.done + max_long) + 15) & ~(uintptr_t)15);
+  a.done = done;
+  a.seg_entry = entry;
   a.partial = part;
   SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
@@ -831,3 +837,23 @@ extern "C" int spmmdb_csrmm_segment(int64_t nnz) {
   if (nnz < (int64_t)32 << 20) return 256;
   return 512;  // B200 sweep on the products-shaped graph: 256 / 512 / 1024 / 2048 -> 4.75 / 4.74 / 4.97 / 5.21 ms
 }
+
+// With long average rows one warp per row is the fast path and a segment shorter than a few average rows
+// would push most of the matrix through the partial-sum path (C3 remainder of a hybrid split: 207 nnz per
+// row, 256-entry segments, 2.4 ms instead of 0.9): at least the power of two above 4 average rows.
+extern "C" int spmmdb_csrmm_segment_for(int m, int64_t nnz) {
+  int seg = spmmdb_csrmm_segment(nnz);
+  if (m > 0 && nnz > 0) {
+    const int64_t want = 4 * ((nnz + m - 1) / m);
+    while (seg < want && seg < (1 << 20)) seg <<= 1;
+  }
+  return seg;
+}
+
+namespace { int g_segment_override = 0; }
+extern "C" int spmmdb_set_csrmm_segment(int seg) {
+  if (seg != 0 && (seg < 32 || (seg & (seg - 1)) != 0)) return SPMMDB_ERR_INVALID_VALUE;
+  g_segment_override = seg;
+  return SPMMDB_OK;
+}
+extern "C" int spmmdb_get_csrmm_segment(void) { return g_segment_override; }

@@ -32,8 +32,16 @@ def _dev(*ts):
             raise ValueError("spmmdb ops take contiguous tensors")
 
 
-def csrmm_segment(nnz):
-    return lib().spmmdb_csrmm_segment(int(nnz))
+def csrmm_segment(nnz, m=None):
+    """Segment length of a call: lower bound by nnz alone, or (with m) the length actually used."""
+    if m is None:
+        return lib().spmmdb_csrmm_segment(int(nnz))
+    return lib().spmmdb_csrmm_segment_for(int(m), int(nnz))
+
+
+def set_csrmm_segment(seg):
+    """Process-wide segment override (0 = automatic); row-sharded runs set the whole matrix's length."""
+    check(lib().spmmdb_set_csrmm_segment(int(seg)), "spmmdb_set_csrmm_segment")
 
 
 def csrmm(rowptr, colind, val, B, C_out, m, k, K, ldb=None, b_layout=ROW_MAJOR, ldc=None, c_layout=ROW_MAJOR,

@@ -43,6 +43,10 @@ def test_binding_covers_header(L):
 def test_version_and_status(L):
     assert b"spmmdb" in L.spmmdb_version()
     assert L.spmmdb_csrmm_segment(1000) == 64 and L.spmmdb_csrmm_segment(62_000_000) == 512
+    # long average rows raise it (4 x 271 -> 2048); the override is validated and process-wide
+    assert L.spmmdb_csrmm_segment_for(132534, 35_950_920) == 2048 and L.spmmdb_csrmm_segment_for(169343, 1_166_243) == 64
+    assert L.spmmdb_set_csrmm_segment(100) == -1 and L.spmmdb_set_csrmm_segment(1024) == 0
+    assert L.spmmdb_get_csrmm_segment() == 1024 and L.spmmdb_set_csrmm_segment(0) == 0
 
 
 def test_validation_without_device(L):

@@ -49,7 +49,7 @@ def test_csrmm_rowmajor_widths(pkg, oracle, K):
     assert err_vs(oracle, got, ref, rp, ci, v, B, K) <= TOL_FP32
     # rows within one segment follow the reference kernel's FMA order exactly
     seq = oracle.csrmm_f32_seq(rp, ci, v, B, K)
-    short = np.diff(rp) <= pkg.csrmm_segment(ci.size)
+    short = np.diff(rp) <= pkg.csrmm_segment(ci.size, m=m)
     assert np.array_equal(got[short], seq[short])
     assert np.all(got[[0, 6, 776]] == 0)  # empty rows are written (gespmm_csrmm.h:133-135)
 
@@ -125,7 +125,11 @@ def test_csrmm_long_rows_are_sharding_independent(pkg, oracle):
     rps = (rp[lo:] - rp[lo]).astype(np.int32)
     cis, vs = ci[rp[lo]:], v[rp[lo]:]
     part = torch.empty(m - lo, K, device="cuda")
-    pkg.csrmm(dev(rps), dev(cis), dev(vs), dB, part, m - lo, k, K, nnz=nnz)  # nnz of the WHOLE matrix fixes seg
+    pkg.set_csrmm_segment(pkg.csrmm_segment(nnz, m=m))  # the whole matrix's segment length
+    try:
+        pkg.csrmm(dev(rps), dev(cis), dev(vs), dB, part, m - lo, k, K)
+    finally:
+        pkg.set_csrmm_segment(0)
     assert torch.equal(part, full[lo:])
 
 
@@ -330,6 +334,26 @@ def test_check_result_harness(pkg, oracle):
     assert float((z1 - z2).abs().max()) < 1e-4
     ref = oracle.csrmm(rp, ci, v, y, dim)
     assert np.max(np.abs(z1.cpu().numpy().T - ref)) < 1e-4
+
+
+@pytest.mark.parametrize("K", [128, 100])
+def test_csrmm_scratch_reuse_across_sizes(pkg, oracle, K):
+    """The long-row queue lives in library scratch whose layout moves with nnz: a call must not trip over
+    what an earlier call with another nnz left there (regression: `done` counters of a small matrix landed on
+    the row records of a bigger one and its hub rows came out wrong)."""
+    rng = np.random.default_rng(77)
+    mats = []
+    for m, avg, hubs in ((3000, 10, {3: 1500, 900: 700, 2999: 300}), (900, 9, {0: 400, 450: 200}),
+                         (2000, 3, {5: 1999, 6: 1000, 7: 500, 1500: 90})):
+        rp, ci, v = random_csr(rng, m, m, avg, hubs=hubs)
+        B = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+        mats.append((m, rp, ci, v, B, oracle.csrmm(rp, ci, v, B, K)))
+    for order in ((0, 1, 2), (2, 1, 0), (1, 0, 1), (0, 2, 0)):
+        for i in order:
+            m, rp, ci, v, B, ref = mats[i]
+            C = torch.full((m, K), float("nan"), device="cuda")
+            pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, m, K)
+            assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32, (order, i)
 
 
 # ----------------------------------------------------------------------------- divide (hybrid split)

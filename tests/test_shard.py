@@ -110,6 +110,10 @@ def test_shards_concatenate_bit_exact_gpu(parts):
         rps, cis, vs = shard.shard_csr(rpd, cid, vd, lo, hi)
         Cs = torch.empty(hi - lo, K, device="cuda")
         if hi > lo:
-            pkg.csrmm(rps, cis, vs, B, Cs, hi - lo, n, K, nnz=nnz)  # nnz of the WHOLE matrix: same segment length
+            pkg.set_csrmm_segment(pkg.csrmm_segment(nnz, m=n))  # the WHOLE matrix's segment length on every shard
+            try:
+                pkg.csrmm(rps, cis, vs, B, Cs, hi - lo, n, K)
+            finally:
+                pkg.set_csrmm_segment(0)
         outs.append(Cs)
     assert torch.equal(torch.cat(outs), full)

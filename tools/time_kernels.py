@@ -74,6 +74,32 @@ def bsr_case(name, rp, ci, val, B, K, bs, maths, flush):
                               gbs=byts / med / 1e6, frac_hbm=byts / med / 1e6 / HBM)), flush=True)
 
 
+def hybrid_case(name, rp, ci, K, bs, densities, math, flush):
+    """divide.cu's idea on the device: dense blocks -> tcgen05 BSR path, the rest -> CSR path, one C."""
+    n, nnz = rp.numel() - 1, ci.numel()
+    mb = (n + bs - 1) // bs
+    val = torch.ones(nnz, device="cuda")
+    Bp = torch.rand(mb * bs, K, device="cuda") * 2 - 1
+    C = torch.zeros(mb * bs, K, device="cuda")
+    med_csr, _ = timeit(lambda: pkg.csrmm(rp, ci, val, Bp, C, n, n, K, nnz=nnz), flush=flush)
+    ref = C.clone()
+    for dens in densities:
+        med_d, _ = timeit(lambda: pkg.divide(n, n, rp, ci, None, bs, dens), warmup=1, iters=3)
+        crp, cci, cv, brp, bci, bv = pkg.divide(n, n, rp, ci, None, bs, dens)
+        nnzb, cnnz = bci.numel(), cci.numel()
+
+        def run():
+            pkg.csrmm(crp, cci, cv, Bp, C, n, n, K, nnz=cnnz)  # beta = 0: C overwritten
+            if nnzb:
+                pkg.bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 1.0, C, K, c_layout=0, math=math)
+        med, best = timeit(run, warmup=2, iters=7, flush=flush)
+        err = float((C[:n] - ref[:n]).abs().max() / ref[:n].abs().max())
+        print(json.dumps(dict(case=name, kernel="hybrid", bs=bs, density=dens, math=math, nnzb=nnzb, csr_nnz=cnnz,
+                              dense_part=1 - cnnz / nnz, block_fill=(nnz - cnnz) / max(nnzb * bs * bs, 1),
+                              ms_hybrid=med, ms_csr_only=med_csr, speedup=med_csr / med, ms_divide=med_d,
+                              useful_gflops=2 * nnz * K / med / 1e6, rel_diff_vs_csr=err)), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", default="c2,c2l,c4,c5,c5l,c3")
@@ -113,6 +139,13 @@ def main():
             val, B, C = csr_case("c3_proteins_pin1", rp, ci, 128, flush)
             for bs in (16, 32):
                 bsr_case("c3_proteins_pin1", rp, ci, val, B, 128, bs, maths, flush)
+        elif case == "c3h":
+            # hybrid split on the community graph as generated (90 % of the edges inside communities) and on a
+            # noisier one (60 %): how much of the matrix the dense path takes and what it buys
+            for p_in in (0.9, 0.6):
+                rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale, p_in=p_in)
+                for bs in (16, 32):
+                    hybrid_case(f"c3_proteins_pin{p_in}", rp, ci, 128, bs, (0.02, 0.05, 0.1, 0.2), 1, flush)
         elif case == "c3":
             rp, ci = graphs.make_config_graph("c3_proteins", device="cuda", scale=a.scale)
             val, B, C = csr_case("c3_proteins_ideal", rp, ci, 128, flush)
