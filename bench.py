@@ -90,6 +90,8 @@ def reference_cpu_run(rp, ci, B, K, steps, warmup, budget_s):
     O.build()
     use_ref = O.ref_spmm_lib() is not None
     fn = O.ref_csr_spmm if use_ref else O.spmm_cc_csr
+    if use_ref:  # all host cores, also under torchrun (which exports OMP_NUM_THREADS=1 to its workers)
+        O.ref_set_omp_threads(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
     cores = O.ref_omp_threads() if use_ref else (os.cpu_count() or 1)
     n = rp.size - 1
     dense = B.astype(np.float64)

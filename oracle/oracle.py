@@ -253,6 +253,13 @@ def ref_omp_threads():
     return int(L.ref_omp_max_threads()) if L is not None else 0
 
 
+def ref_set_omp_threads(n):
+    """Give the reference's OpenMP loop n threads (torchrun exports OMP_NUM_THREADS=1 to its workers)."""
+    L = ref_spmm_lib()
+    if L is not None and hasattr(L, "ref_omp_set_threads"):
+        L.ref_omp_set_threads(int(n))
+
+
 def ref_calculate_nnzb(rowptr, colind, bs):
     L = ref_host_lib()
     rowptr, colind = _i32(rowptr), _i32(colind)

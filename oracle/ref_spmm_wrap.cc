@@ -25,5 +25,6 @@ void ref_coo_spmm(int64_t rows, int64_t cols, int64_t nnz, int64_t K,
 }
 
 int ref_omp_max_threads() { return omp_get_max_threads(); }
+void ref_omp_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 }  // extern "C"
