@@ -93,6 +93,15 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t addr, int cols) {
   if (cols == 256) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(addr) : "memory");
   else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(addr) : "memory");
 }
+// elect.sync: exactly one lane of the (converged) warp gets true, and ptxas KNOWS the guarded region runs on
+// one lane -- with `lane == 0` it does not, and wraps every tcgen05.mma in an ELECT / R2UR.BROADCAST /
+// BRA.U.ANY loop over the distinct operand values it fears the lanes might hold.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
@@ -413,16 +422,19 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
             m &= ~((len >= 32 ? 0xffffffffu : ((1u << len) - 1u)) << l0);
             const uint32_t idesc = idesc_base | (((uint32_t)(len * a.bs) >> 3) << 17);
             const uint32_t b_lo0 = ((sA16 + (((uint32_t)l0 * a.block_bytes) >> 4)) & 0x3fffu) | b_lo_fixed;
-            for (int t = 0; t < a.tiles; ++t) {
-              const uint32_t d = dcol + (uint32_t)(t * a.NT + l0 * a.bs);
-              const uint32_t a_lo0 = (((sB + (uint32_t)(t * CPT) * a.chunk_bytes) >> 4) & 0x3fffu) | a_lo_fixed;
-              for (int ks = 0; ks < ksteps; ++ks) {
-                const uint64_t adesc = ((uint64_t)a_hi << 32) | (a_lo0 + (uint32_t)ks * a_kstep);
-                const uint64_t bdesc = ((uint64_t)b_hi << 32) | (b_lo0 + (uint32_t)ks * b_kstep);
-                // tcgen05.mma has per-thread semantics: exactly one lane may issue it
-                if (leader) umma<BF16>(d, adesc, bdesc, idesc, (tb | (ks > 0)) ? 1u : 0u);
+            // tcgen05.mma has per-thread semantics: exactly one lane may issue it
+            if (elect_one()) {
+              for (int t = 0; t < a.tiles; ++t) {
+                const uint32_t d = dcol + (uint32_t)(t * a.NT + l0 * a.bs);
+                const uint32_t a_lo0 = (((sB + (uint32_t)(t * CPT) * a.chunk_bytes) >> 4) & 0x3fffu) | a_lo_fixed;
+                for (int ks = 0; ks < ksteps; ++ks) {
+                  const uint64_t adesc = ((uint64_t)a_hi << 32) | (a_lo0 + (uint32_t)ks * a_kstep);
+                  const uint64_t bdesc = ((uint64_t)b_hi << 32) | (b_lo0 + (uint32_t)ks * b_kstep);
+                  umma<BF16>(d, adesc, bdesc, idesc, (tb | (ks > 0)) ? 1u : 0u);
+                }
               }
             }
+            __syncwarp();
           }
           touched |= mask;
           if (leader) {
