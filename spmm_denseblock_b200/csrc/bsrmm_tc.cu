@@ -361,7 +361,9 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       uint32_t acc_phase[2] = {0, 0};
       const uint32_t rp = (uint32_t)a.bs * ESIZE;  // row pitch of a block in shared memory
       const uint32_t a_layout = rp == 128 ? kLayoutSw128 : (rp == 64 ? kLayoutSw64 : kLayoutSw32);
-      const uint32_t idesc_base = (1u << 4) | (FMT << 7) | (FMT << 10) | (1u << 15) |
+      // dbg & 64: timing experiment only (wrong results) -- describe the slab as a K-major operand
+      const bool kmaj_exp = (a.dbg & 64) != 0;
+      const uint32_t idesc_base = (1u << 4) | (FMT << 7) | (FMT << 10) | ((kmaj_exp ? 0u : 1u) << 15) |
                                   ((a.dir == SPMMDB_DIR_COLUMN ? 1u : 0u) << 16) | ((128u >> 4) << 24);
       const int ksteps = a.bs / KI;
       const int max_run = 256 / a.bs;
@@ -369,9 +371,10 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       // MMA operand A = B slab, MN-major: 128-byte feature chunks LBO apart, k groups SBO apart
       //   bf16: SWIZZLE_128B, groups of 8 k rows (1024 B); tf32: 32-bit MN-major operands exist only in
       //   the 128B-swizzle-with-32B-atoms layout, groups of 4 k rows (512 B)
-      const uint32_t a_hi = ((BF16 ? 1024u : 512u) >> 4) | (1u << 14) | ((BF16 ? kLayoutSw128 : kLayoutSw128B32) << 29);
-      const uint32_t a_lo_fixed = ((a.chunk_bytes >> 4) & 0x3fffu) << 16;
-      const uint32_t a_kstep = (uint32_t)(KI * 128) >> 4;  // KI rows of 128 B per k-step
+      const uint32_t a_hi = kmaj_exp ? ((1024u >> 4) | (1u << 14) | (kLayoutSw128 << 29))
+                                     : (((BF16 ? 1024u : 512u) >> 4) | (1u << 14) | ((BF16 ? kLayoutSw128 : kLayoutSw128B32) << 29));
+      const uint32_t a_lo_fixed = kmaj_exp ? (1u << 16) : (((a.chunk_bytes >> 4) & 0x3fffu) << 16);
+      const uint32_t a_kstep = kmaj_exp ? 2u : ((uint32_t)(KI * 128) >> 4);  // KI rows of 128 B per k-step
       // MMA operand B = A strip.  DIR_ROW: K-major, advance 32 B inside the swizzle atom per k-step,
       //   8-row groups SBO = 8 * rp apart.  DIR_COLUMN: MN-major, blocks LBO apart, k groups 8 * rp apart.
       const uint32_t b_hi = ((8u * rp) >> 4) | (1u << 14) | (a_layout << 29);
@@ -437,7 +440,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
             __syncwarp();
           }
           touched |= mask;
-          if (leader) {
+          if (elect_one()) {
             if (a.dbg & 8) mbar_arrive(&ctl->empty[stage]);
             else umma_commit(&ctl->empty[stage]);  // frees the stage when these MMAs have read it
           }
