@@ -235,7 +235,7 @@ def main():
     if os.path.exists(tp) and world == 1 and a.scale == 1.0:
         traffic = json.load(open(tp)).get(a.workload)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "csrmm_stream_kernel (+csrmm_long_kernel)", "peak_source": peak_src,
+                "traffic": traffic, "kernel": "csrmm_stream_kernel (queued long-row segments taken between items)", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes,
                 "gather_bytes_per_launch": 4 * nnzs * K,
                 "note": "B-row gathers (nnz*K*4 B) are served by L2/L1, not counted as algorithmic bytes"}
