@@ -166,6 +166,28 @@ int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const int* colin
                       const int* csr_rowptr, int* csr_colind, float* csr_val, void* stream);
 
 /* --------------------------------------------------------------------------
+ * Apply a node permutation on the device (the reordering algorithms themselves stay on
+ * the CPU and only produce old2new; one new id per old id, a bijection of 0..n-1).
+ *   spmmdb_permute_csr_f32   A' = P A P^T, replaces permutate + sortNeighbors
+ *                            (reorder_strategy.cc:15-39): column j -> old2new[j], row i -> position
+ *                            old2new[i], every row re-sorted ascending.  val / new_val may both be NULL
+ *                            (the reference's adjacency lists carry no values); values follow their
+ *                            entries.  Writes new_rowptr[n+1], new_colind[nnz]; synchronises `stream`.
+ *   spmmdb_permute_rows_f32  out[old2new[r]][0..K) = in[r][0..K): the feature rows of B (or C back
+ *                            with the inverse permutation) in the new numbering; out != in.
+ *   spmmdb_heatmap           heat[(i / bs) * nb + j / bs] += 1 per non-zero, nb = ceil(n / bs),
+ *                            heat cleared first: getHeatmap (utility.cc:71-88; the reference uses 256).
+ * Block counts / density / utilisation (calculateNnzb utility.cc:47-69, reorder_graph.cc:12-24)
+ * are spmmdb_csr2bsr_nnz's nnzb:  density = nnzb / nb^2, utilisation = nnz / (nnzb * bs^2).
+ * ------------------------------------------------------------------------ */
+int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colind, const float* val,
+                           const int* old2new, int* new_rowptr, int* new_colind, float* new_val,
+                           void* stream);
+int spmmdb_permute_rows_f32(int rows, int K, const float* in, int64_t ldi, const int* old2new,
+                            float* out, int64_t ldo, void* stream);
+int spmmdb_heatmap(int n, const int* rowptr, const int* colind, int block_dim, int* heat, void* stream);
+
+/* --------------------------------------------------------------------------
  * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all
  * pointers are HOST pointers (pinned memory gives full PCIe rate).  Copies A and
  * B to the device, runs the device path, copies C back and synchronises -- the

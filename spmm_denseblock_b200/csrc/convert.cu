@@ -417,6 +417,10 @@ int launch_csr2bsr(int dir, int m, int mb, int bs, const int* rowptr, const int*
 }
 
 }  // namespace
+
+int exclusive_scan_i32(const int* counts, int n, int* sums, int* out, cudaStream_t st) {
+  return exclusive_scan(counts, n, sums, out, st);
+}
 }  // namespace spmmdb
 
 using namespace spmmdb;

@@ -158,3 +158,45 @@ def divide(m, n, rowptr, colind, val, block_dim, density, direction=DIR_ROW):
                                  _p(csr_val), _stream())
     check(rc, "spmmdb_divide_f32")
     return csr_rowptr, csr_colind, csr_val, bsr_rowptr, bsr_colind, bsr_val
+
+
+def permute_csr(rowptr, colind, val, old2new):
+    """A' = P A P^T (permutate, reorder_strategy.cc:26-39) on the device.  Returns (rowptr, colind, val)."""
+    _dev(rowptr, colind, val, old2new)
+    n = rowptr.numel() - 1
+    nrp = torch.empty(n + 1, dtype=torch.int32, device=rowptr.device)
+    nci = torch.empty(colind.numel(), dtype=torch.int32, device=rowptr.device)
+    nv = torch.empty(colind.numel(), dtype=torch.float32, device=rowptr.device) if val is not None else None
+    rc = lib().spmmdb_permute_csr_f32(n, _p(rowptr), _p(colind), _p(val), _p(old2new), _p(nrp), _p(nci), _p(nv),
+                                      _stream())
+    check(rc, "spmmdb_permute_csr_f32")
+    return nrp, nci, nv
+
+
+def permute_rows(X, old2new):
+    """out[old2new[r]] = X[r] for a row-major dense matrix."""
+    _dev(X, old2new)
+    out = torch.empty_like(X)
+    rows, K = X.shape
+    check(lib().spmmdb_permute_rows_f32(rows, K, _p(X), K, _p(old2new), _p(out), K, _stream()),
+          "spmmdb_permute_rows_f32")
+    return out
+
+
+def heatmap(rowptr, colind, block_dim=256):
+    """getHeatmap (utility.cc:71-88): non-zeros per block_dim x block_dim block, nb x nb int32."""
+    _dev(rowptr, colind)
+    n = rowptr.numel() - 1
+    nb = (n + block_dim - 1) // block_dim
+    heat = torch.empty(nb, nb, dtype=torch.int32, device=rowptr.device)
+    check(lib().spmmdb_heatmap(n, _p(rowptr), _p(colind), block_dim, _p(heat), _stream()), "spmmdb_heatmap")
+    return heat
+
+
+def block_metrics(rowptr, colind, block_dim):
+    """analyzeBlockSparseMetrics (reorder_graph.cc:12-24): (nnzb, density, utilization, average)."""
+    n, nnz = rowptr.numel() - 1, colind.numel()
+    nb = (n + block_dim - 1) // block_dim
+    tmp = torch.empty(nb + 1, dtype=torch.int32, device=rowptr.device)
+    nnzb = csr2bsr_nnz(n, n, rowptr, colind, block_dim, tmp)
+    return nnzb, nnzb / (nb * nb), nnz / (nnzb * block_dim * block_dim), nnz / nnzb

@@ -461,3 +461,85 @@ def test_divide_full_size_proteins_property(pkg):
     bdeg = (brp[1:] - brp[:-1]).long()
     blk_key = torch.arange(mb, device="cuda").repeat_interleave(bdeg) * mb + bci.long()
     assert not torch.isin(rem_key, blk_key).any()
+
+
+# ----------------------------------------------------------------------------- permutation on the device
+def test_permute_golden_reference(pkg, golden_dir):
+    """GPU permutation against the output of the reference's OWN permutate (reorder_strategy.cc:26-39,
+    fixture made by tests/golden/make_golden.py): bit-exact."""
+    import os
+    d = np.load(os.path.join(golden_dir, "ref_permutate.npz"))
+    nrp, nci, nv = pkg.permute_csr(dev(d["rowptr"]), dev(d["colind"]), None, dev(d["old2new"]))
+    assert nv is None
+    assert np.array_equal(nrp.cpu().numpy(), d["p_rowptr"]) and np.array_equal(nci.cpu().numpy(), d["p_colind"])
+
+
+@pytest.mark.parametrize("n,avg,hubs", [(700, 5, {}), (3000, 20, {5: 40, 9: 1000, 11: 1025, 77: 2999}),
+                                        (40000, 3, {123: 16384, 9000: 16385, 39999: 33000})])
+def test_permute_csr_bit_exact_with_values(pkg, oracle, n, avg, hubs):
+    """All row-length classes (warp, shared-memory CTA small / large, global staging), values follow entries."""
+    rng = np.random.default_rng(n)
+    rp, ci, v = random_csr(rng, n, n, avg, hubs=hubs, empty_rows={1, n - 1})
+    perm = rng.permutation(n).astype(np.int32)
+    nrp, nci, nv = pkg.permute_csr(dev(rp), dev(ci), dev(v), dev(perm))
+    orp, oci = oracle.permutate_csr(rp, ci, perm)
+    assert np.array_equal(nrp.cpu().numpy(), orp) and np.array_equal(nci.cpu().numpy(), oci)
+    # values: A'[perm[i], perm[j]] == A[i, j]
+    import scipy.sparse as sp
+    A = sp.csr_matrix((v, ci, rp), shape=(n, n))
+    Ap = sp.csr_matrix((nv.cpu().numpy(), nci.cpu().numpy(), nrp.cpu().numpy()), shape=(n, n))
+    inv = np.empty(n, np.int64)
+    inv[perm] = np.arange(n)
+    back = Ap[perm][:, perm].tocsr()
+    back.sort_indices()
+    assert np.array_equal(back.indptr, rp) and np.array_equal(back.indices, ci) and np.array_equal(back.data, v)
+
+
+def test_permute_rows_heatmap_metrics_and_spmm_invariance(pkg, oracle):
+    """P (A B) = (P A P^T)(P B): SpMM on the permuted operands, un-permuted, equals the original product;
+    heat map and block metrics equal the reference definitions (utility.cc:47-88, reorder_graph.cc:12-24)."""
+    rng = np.random.default_rng(4)
+    n, K, bs = 2500, 64, 16
+    rp, ci, v = random_csr(rng, n, n, 7, hubs={3: 900})
+    perm = rng.permutation(n).astype(np.int32)
+    inv = np.empty(n, np.int32)
+    inv[perm] = np.arange(n, dtype=np.int32)
+    B = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    nrp, nci, nv = pkg.permute_csr(dev(rp), dev(ci), dev(v), dev(perm))
+    Bp = pkg.permute_rows(dev(B), dev(perm))
+    assert np.array_equal(Bp.cpu().numpy()[perm], B)
+    Cp = torch.empty(n, K, device="cuda")
+    pkg.csrmm(nrp, nci, nv, Bp, Cp, n, n, K)
+    C = pkg.permute_rows(Cp, dev(inv)).cpu().numpy()
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    assert err_vs(oracle, C, ref, rp, ci, v, B, K) <= TOL_FP32
+    heat = pkg.heatmap(dev(rp), dev(ci), 256).cpu().numpy()
+    nb = (n + 255) // 256
+    want = np.zeros((nb, nb), np.int64)
+    rows = np.repeat(np.arange(n), np.diff(rp))
+    np.add.at(want, (rows // 256, ci // 256), 1)
+    assert np.array_equal(heat, want)
+    nnzb, density, util, average = pkg.block_metrics(dev(rp), dev(ci), bs)
+    assert nnzb == oracle.calculate_nnzb(rp, ci, bs)
+    nbb = (n + bs - 1) // bs
+    assert density == nnzb / (nbb * nbb) and util == ci.size / (nnzb * bs * bs) and average == ci.size / nnzb
+
+
+def test_permute_full_size_products_property(pkg):
+    """Size-independent properties at the C5 (products-shaped) size: rows sorted, degrees moved, the inverse
+    permutation restores the matrix bit for bit."""
+    from spmm_denseblock_b200 import graphs
+    rp, ci = graphs.make_config_graph("c5_products", device="cuda", scale=0.5)
+    n = rp.numel() - 1
+    g = torch.Generator(device="cuda").manual_seed(5)
+    perm = torch.randperm(n, generator=g, device="cuda").to(torch.int32)
+    inv = torch.empty_like(perm)
+    inv[perm.long()] = torch.arange(n, device="cuda", dtype=torch.int32)
+    nrp, nci, _ = pkg.permute_csr(rp, ci, None, perm)
+    deg, ndeg = rp[1:] - rp[:-1], nrp[1:] - nrp[:-1]
+    assert torch.equal(ndeg[perm.long()], deg)
+    same_row = torch.ones(nci.numel() - 1, dtype=torch.bool, device="cuda")
+    same_row[(nrp[1:-1].long() - 1).clamp_(min=0)] = False  # last entry of a row vs first of the next
+    assert bool(((nci[1:] > nci[:-1]) | ~same_row).all())
+    brp, bci, _ = pkg.permute_csr(nrp, nci, None, inv)
+    assert torch.equal(brp, rp) and torch.equal(bci, ci)

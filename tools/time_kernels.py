@@ -139,6 +139,24 @@ def main():
             val, B, C = csr_case("c3_proteins_pin1", rp, ci, 128, flush)
             for bs in (16, 32):
                 bsr_case("c3_proteins_pin1", rp, ci, val, B, 128, bs, maths, flush)
+        elif case == "perm":
+            # permutation application on the device (permutate, reorder_strategy.cc:26-39) + heat map
+            for name, K in (("c5_products", 256), ("c3_proteins", 128), ("c2_arxiv", 128)):
+                rp, ci = graphs.make_config_graph(name, device="cuda", scale=a.scale)
+                n, nnz = rp.numel() - 1, ci.numel()
+                perm = torch.randperm(n, device="cuda").to(torch.int32)
+                val = torch.ones(nnz, device="cuda")
+                X = torch.rand(n, K, device="cuda")
+                m1, _ = timeit(lambda: pkg.permute_csr(rp, ci, val, perm), warmup=1, iters=3)
+                m2, _ = timeit(lambda: pkg.permute_rows(X, perm), warmup=1, iters=3)
+                m3, _ = timeit(lambda: pkg.heatmap(rp, ci, 256), warmup=1, iters=3)
+                b1 = 8 * (n + 1) + 4 * n + 16 * nnz + 4 * nnz  # rowptr in/out, old2new, (col, val) in/out, old2new gathers
+                print(json.dumps(dict(case=name, kernel="permute_csr", n=n, nnz=nnz, ms_med=m1, gbs=b1 / m1 / 1e6,
+                                      frac=b1 / m1 / 1e6 / HBM, maxdeg=int((rp[1:] - rp[:-1]).max()),
+                                      permute_rows_ms=m2, permute_rows_gbs=8 * n * K / m2 / 1e6, heatmap256_ms=m3)),
+                      flush=True)
+                del X, val
+                torch.cuda.empty_cache()
         elif case == "c3h":
             # hybrid split on the community graph as generated (90 % of the edges inside communities) and on a
             # noisier one (60 %): how much of the matrix the dense path takes and what it buys
