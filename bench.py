@@ -277,7 +277,7 @@ def main():
     d2h = 4 * ms_ * K
     e2e = {"value": 2.0 * nnz * K / (e2e_ms * 1e-3) / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "matches_device_path": bool(e2e_ok),
-           "api": "spmmdb_csrmm_host_f32 (pinned host buffers)"}
+           "api": "spmmdb_csrmm_host_f32 (pinned host buffers; feature slabs pipelined over H2D / kernel / D2H)"}
 
     out = {"metric": "SpMM GFLOP/s (2*nnz*K/t)", "value": value, "unit": "GFLOP/s", "n_gpus": world,
            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,

@@ -1,6 +1,8 @@
 // host.cu -- host-buffer entry points: what a caller that keeps its matrices in
 // host memory (the reference drivers' state before their cudaMemcpy block,
 // run_csrmm.cu:94-116) calls.  Copies in, runs the device path, copies out.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 using namespace spmmdb;
@@ -30,14 +32,67 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
     SPMMDB_CUDA_OK(cudaMemcpyAsync(d_colind, h_colind, sizeof(int) * (size_t)nnz, cudaMemcpyHostToDevice, st));
     SPMMDB_CUDA_OK(cudaMemcpyAsync(d_val, h_val, sizeof(float) * (size_t)nnz, cudaMemcpyHostToDevice, st));
   }
-  SPMMDB_CUDA_OK(cudaMemcpyAsync(dB, h_B, b_bytes, cudaMemcpyHostToDevice, st));
-  if (beta != 0.f) SPMMDB_CUDA_OK(cudaMemcpyAsync(dC, h_C, c_bytes, cudaMemcpyHostToDevice, st));
-  int rc = spmmdb_csrmm_f32(m, k, K, nnz, d_rowptr, d_colind, d_val, dB, K, SPMMDB_ROW_MAJOR, dC, K,
-                            SPMMDB_ROW_MAJOR, alpha, beta, st);
-  if (rc != SPMMDB_OK) return rc;
-  SPMMDB_CUDA_OK(cudaMemcpyAsync(h_C, dC, c_bytes, cudaMemcpyDeviceToHost, st));
-  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
-  return SPMMDB_OK;
+  // Feature slabs: columns [c0, c0 + Ks) of C need only the same columns of B, so the host<->device copies of one
+  // slab overlap the kernel and the opposite-direction copy of its neighbours (PCIe is full duplex): the call costs
+  // about H2D(A) + H2D(B) + D2H(one slab) instead of H2D(A) + H2D(B) + kernel + D2H(C).
+  static const int slabs_env = [] { const char* e = getenv("SPMMDB_HOST_SLABS"); return e ? atoi(e) : 0; }();
+  int slabs = slabs_env > 0 ? slabs_env : 4;
+  while (slabs > 1 && (K % slabs != 0 || (K / slabs) % 64 != 0)) slabs >>= 1;  // >= 256-byte rows for the DMA engines
+  if (slabs <= 1) {
+    SPMMDB_CUDA_OK(cudaMemcpyAsync(dB, h_B, b_bytes, cudaMemcpyHostToDevice, st));
+    if (beta != 0.f) SPMMDB_CUDA_OK(cudaMemcpyAsync(dC, h_C, c_bytes, cudaMemcpyHostToDevice, st));
+    int rc = spmmdb_csrmm_f32(m, k, K, nnz, d_rowptr, d_colind, d_val, dB, K, SPMMDB_ROW_MAJOR, dC, K,
+                              SPMMDB_ROW_MAJOR, alpha, beta, st);
+    if (rc != SPMMDB_OK) return rc;
+    SPMMDB_CUDA_OK(cudaMemcpyAsync(h_C, dC, c_bytes, cudaMemcpyDeviceToHost, st));
+    SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+    return SPMMDB_OK;
+  }
+  // `st` carries the H2D copies (A is already queued on it), a second stream the kernels, a third the D2H copies
+  static thread_local cudaStream_t s_run = nullptr, s_out = nullptr;
+  static thread_local cudaEvent_t ev_in[16], ev_run[16];
+  static thread_local bool ev_made = false;
+  if (slabs > 16) slabs = 16;
+  if (s_run == nullptr) {
+    SPMMDB_CUDA_OK(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
+    SPMMDB_CUDA_OK(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+  }
+  if (!ev_made) {
+    for (int i = 0; i < 16; ++i) {
+      SPMMDB_CUDA_OK(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+      SPMMDB_CUDA_OK(cudaEventCreateWithFlags(&ev_run[i], cudaEventDisableTiming));
+    }
+    ev_made = true;
+  }
+  const int Ks = K / slabs;
+  const size_t pitch = sizeof(float) * (size_t)K, width = sizeof(float) * (size_t)Ks;
+  // the kernels of all slabs share the whole call's segment length (same bits as the one-shot call)
+  const int seg_before = spmmdb_get_csrmm_segment();
+  if (seg_before == 0) spmmdb_set_csrmm_segment(spmmdb_csrmm_segment_for(m, nnz));
+  int rc = SPMMDB_OK;
+  for (int sl = 0; sl < slabs && rc == SPMMDB_OK; ++sl) {
+    const size_t off = (size_t)sl * Ks;
+    cudaError_t e = cudaMemcpy2DAsync(dB + off, pitch, h_B + off, pitch, width, (size_t)k, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && beta != 0.f)
+      e = cudaMemcpy2DAsync(dC + off, pitch, h_C + off, pitch, width, (size_t)m, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_in[sl], st);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_run, ev_in[sl], 0);
+    if (e != cudaSuccess) { set_last_error("host slab copy", e, __FILE__, __LINE__); rc = SPMMDB_ERR_CUDA; break; }
+    rc = spmmdb_csrmm_f32(m, k, Ks, nnz, d_rowptr, d_colind, d_val, dB + off, K, SPMMDB_ROW_MAJOR, dC + off, K,
+                          SPMMDB_ROW_MAJOR, alpha, beta, s_run);
+    if (rc != SPMMDB_OK) break;
+    e = cudaEventRecord(ev_run[sl], s_run);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, ev_run[sl], 0);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(h_C + off, pitch, dC + off, pitch, width, (size_t)m, cudaMemcpyDeviceToHost, s_out);
+    if (e != cudaSuccess) { set_last_error("host slab copy", e, __FILE__, __LINE__); rc = SPMMDB_ERR_CUDA; }
+  }
+  if (seg_before == 0) spmmdb_set_csrmm_segment(0);
+  cudaStreamSynchronize(st);
+  cudaStreamSynchronize(s_run);
+  cudaError_t e = cudaStreamSynchronize(s_out);
+  if (rc == SPMMDB_OK && e != cudaSuccess) { set_last_error("host slab sync", e, __FILE__, __LINE__); rc = SPMMDB_ERR_CUDA; }
+  return rc;
 }
 
 extern "C" int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds) {

@@ -356,6 +356,28 @@ def test_csrmm_scratch_reuse_across_sizes(pkg, oracle, K):
             assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32, (order, i)
 
 
+@pytest.mark.parametrize("K,alpha,beta", [(256, 1.0, 0.0), (256, 0.5, 2.0), (128, 1.0, 0.0), (100, 1.0, 0.0)])
+def test_csrmm_host_entry_slab_pipeline(pkg, oracle, K, alpha, beta):
+    """spmmdb_csrmm_host_f32 (host buffers; feature slabs copied / computed / copied back in a pipeline when
+    K allows) returns the bits of the device call on the same inputs."""
+    import ctypes as C
+    rng = np.random.default_rng(K)
+    m = 5000
+    rp, ci, v = random_csr(rng, m, m, 8, hubs={17: 3000, 4000: 700})
+    B = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    hC = C0.copy()
+    L = pkg.lib()
+    p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+    rc = L.spmmdb_csrmm_host_f32(m, m, K, ci.size, p(rp), p(ci), p(v), p(B), p(hC), alpha, beta, C.c_void_p(0))
+    assert rc == 0
+    dC = dev(C0)
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), dC, m, m, K, alpha=alpha, beta=beta)
+    assert np.array_equal(hC, dC.cpu().numpy())
+    ref = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=alpha, beta=beta)
+    assert np.max(np.abs(hC - ref)) <= 1e-3
+
+
 # ----------------------------------------------------------------------------- divide (hybrid split)
 def _banded_graph(rng, n, band=16, p_dense=0.7, avg=4):
     rows = []
