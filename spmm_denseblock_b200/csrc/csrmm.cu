@@ -781,7 +781,8 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.partial = part;
   SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
-  const int long_ctas = nsm * 2;
+  static const int lc_env = [] { const char* e = getenv("SPMMDB_CSR_LONG_CTAS"); return e ? atoi(e) : 0; }();
+  const int long_ctas = nsm * (lc_env > 0 ? lc_env : 4);  // C2 sweep: 2 / 4 / 8 -> 0.166 / 0.160 / 0.156 ms
   const bool vec4 = (K % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
                     (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
   static const int stream_min_k = [] { const char* e = getenv("SPMMDB_CSR_STREAM_MIN_K"); return e ? atoi(e) : 32; }();
