@@ -729,11 +729,15 @@ int launch_variant(const CsrArgs& a, int long_ctas, cudaStream_t st) {
 }
 
 template <typename V>
-int dispatch(const CsrArgs& a, int long_ctas, cudaStream_t st) {
+int dispatch(const CsrArgs& a, int long_ctas, bool two_rows, cudaStream_t st) {
   const int nvec = (a.K + VecOps<V>::W - 1) / VecOps<V>::W;
   if (nvec <= 4) return launch_variant<V, 4, 1, 4>(a, long_ctas, st);
   if (nvec <= 8) return launch_variant<V, 8, 1, 8>(a, long_ctas, st);
   if (nvec <= 16) return launch_variant<V, 16, 1, 8>(a, long_ctas, st);
+  // two rows per warp (16 lanes x 2 vectors): a quarter fewer instructions per non-zero than one row per warp, used
+  // for small short-row matrices where the call is latency / issue bound (C2: 0.154 -> 0.141 ms against the
+  // stream kernel, 0.190 for one row per warp; four rows per warp lose to imbalance inside the warp)
+  if (nvec <= 32 && two_rows) return launch_variant<V, 16, 2, 4>(a, long_ctas, st);
   if (nvec <= 32) return launch_variant<V, 32, 1, 8>(a, long_ctas, st);
   if (nvec <= 64) return launch_variant<V, 32, 2, 8>(a, long_ctas, st);
   if (nvec <= 96) return launch_variant<V, 32, 3, 4>(a, long_ctas, st);
@@ -789,7 +793,9 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   // Long average rows (C3: 271 nnz/row) keep one warp per row: the rows kernel reaches the L2 gather
   // ceiling there (0.94 ms vs 1.67 ms for the stream kernel, same profile file).
   const bool dense_rows = m > 0 && nnz / m >= 64;
-  if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows) {
+  // small matrices with a 128-wide dense side: the two-rows-per-warp rows kernel (see dispatch)
+  const bool small_k128 = vec4 && nnz < ((int64_t)4 << 20) && K > 64 && K <= 128 && !dense_rows;
+  if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows && !small_k128) {
     // rows per item: measured on B200 (profiles/r1b_csr_rpi_sweep.txt): 8 rows is the best or within 3% of it
     // for avg degree 2 (C4), 6.5 (C2) and 24 (C5); fewer rows per item for denser rows.
     const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;
@@ -826,7 +832,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     return launch_stream<4, 2, 3>(a, nsm, long_ctas, st);
   }
   a.rpi = 0;
-  return vec4 ? dispatch<float4>(a, long_ctas, st) : dispatch<float>(a, long_ctas, st);
+  return vec4 ? dispatch<float4>(a, long_ctas, small_k128, st) : dispatch<float>(a, long_ctas, false, st);
 }
 
 }  // namespace spmmdb
