@@ -49,6 +49,10 @@ typedef enum {
 #define SPMMDB_MATH_FP32 0   /* CUDA-core fp32 FMA, fp32 accumulate (exact path)    */
 #define SPMMDB_MATH_TF32 1   /* tcgen05 kind::tf32, fp32 accumulate in TMEM         */
 #define SPMMDB_MATH_BF16 2   /* tcgen05 kind::f16 (bf16 inputs), fp32 accumulate    */
+#define SPMMDB_MATH_BF16_PACKED 3 /* as _BF16, but bsr_val already points at bf16 blocks
+                                     made once by spmmdb_bsr_pack_bf16 (same block order and
+                                     direction): half the A stream per call, no per-call
+                                     conversion.  Unit adjacency weights are exact in bf16. */
 
 /* Library / build information. */
 const char* spmmdb_version(void);
@@ -104,6 +108,11 @@ int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, 
                      float alpha, const float* bsr_val, const int* bsr_rowptr,
                      const int* bsr_colind, const float* B, int64_t ldb, float beta, float* C,
                      int64_t ldc, int c_layout, int math, void* stream);
+
+/* fp32 blocks -> bf16 blocks for SPMMDB_MATH_BF16_PACKED (nnzb * block_dim^2 values, round to nearest even);
+ * out_bf16 holds 2 bytes per value, both pointers 16-byte aligned.  With _PACKED the tensor-core shapes
+ * (block_dim 16 / 32 / 64) are the only ones served: others return SPMMDB_ERR_NOT_SUPPORTED. */
+int spmmdb_bsr_pack_bf16(int64_t nnzb, int block_dim, const float* bsr_val, void* out_bf16, void* stream);
 
 /* Process-wide default arithmetic of the drop-in rocsparse_bsrmm_template<>
  * (its signature has no `math` argument).  Initial value: the SPMMDB_BSRMM_MATH

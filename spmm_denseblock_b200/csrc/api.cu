@@ -14,6 +14,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
              int c_layout, int math, cudaStream_t st);
 bool bsrmm_tc_supported(int trans_b, int n, int bs, int64_t ldb, const float* B, const float* val, int c_layout,
                         int64_t ldc, const float* C);
+int bsr_pack_bf16(int64_t elems, const float* in, void* out, cudaStream_t st);
 
 namespace {
 
@@ -131,7 +132,8 @@ extern "C" int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int
   if (trans_b == 0 ? ldb < (int64_t)kb * block_dim : ldb < n) return SPMMDB_ERR_INVALID_VALUE;
   if (c_layout == SPMMDB_COL_MAJOR ? ldc < m : ldc < n) return SPMMDB_ERR_INVALID_VALUE;
   if (c_layout != SPMMDB_COL_MAJOR && c_layout != SPMMDB_ROW_MAJOR) return SPMMDB_ERR_INVALID_VALUE;
-  if (math != SPMMDB_MATH_FP32 && math != SPMMDB_MATH_TF32 && math != SPMMDB_MATH_BF16)
+  if (math != SPMMDB_MATH_FP32 && math != SPMMDB_MATH_TF32 && math != SPMMDB_MATH_BF16 &&
+      math != SPMMDB_MATH_BF16_PACKED)
     return SPMMDB_ERR_INVALID_VALUE;
   if (alpha == 0.f && beta == 1.f) return SPMMDB_OK;  // rocsparse_bsrmm.h:76-78
   const int sm = device_sm();
@@ -144,6 +146,7 @@ extern "C" int spmmdb_bsrmm_f32(int dir, int trans_b, int mb, int n, int kb, int
     // a shape the tensor-core kernel does not lay out (tf32 with 64-wide blocks) runs the fp32 kernel
     if (rc != SPMMDB_ERR_NOT_SUPPORTED) return rc;
   }
+  if (math == SPMMDB_MATH_BF16_PACKED) return SPMMDB_ERR_NOT_SUPPORTED;  // bf16 blocks: tensor-core shapes only
   return bsrmm_simt(dir, trans_b, mb, n, block_dim, alpha, bsr_val, bsr_rowptr, bsr_colind, B, ldb, beta, C, ldc,
                     c_layout, st);
 }
@@ -156,4 +159,13 @@ extern "C" int spmmdb_block_gemm_f32(int mb, int dim, int64_t nnzb, int block_di
   const int64_t m = (int64_t)mb * block_dim;
   return spmmdb_bsrmm_f32(SPMMDB_DIR_COLUMN, /*trans_b=*/1, mb, dim, /*kb=*/mb > 0 ? mb : 1, nnzb, block_dim, 1.0f,
                           bsr_val, bsr_rowptr, bsr_colind, Y, dim, 1.0f, Z, m, SPMMDB_COL_MAJOR, math, stream);
+}
+
+extern "C" int spmmdb_bsr_pack_bf16(int64_t nnzb, int block_dim, const float* bsr_val, void* out_bf16, void* stream) {
+  if (nnzb < 0 || block_dim <= 0 || (block_dim * block_dim) % 4 != 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (nnzb == 0) return SPMMDB_OK;
+  if (bsr_val == nullptr || out_bf16 == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (((uintptr_t)bsr_val | (uintptr_t)out_bf16) % 16 != 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  return bsr_pack_bf16(nnzb * block_dim * block_dim, bsr_val, out_bf16, (cudaStream_t)stream);
 }

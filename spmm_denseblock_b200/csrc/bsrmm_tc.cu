@@ -674,7 +674,8 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
     }
     return SPMMDB_OK;
   }
-  bool bf16 = (math == SPMMDB_MATH_BF16);
+  const bool packed = (math == SPMMDB_MATH_BF16_PACKED);  // `val` already points at bf16 blocks
+  bool bf16 = (math == SPMMDB_MATH_BF16) || packed;
   if (!bf16 && bs == 64) bf16 = false;  // tf32 with 256-byte block rows: see below
   const int esize = bf16 ? 2 : 4;
   if (bs * esize > 128) {
@@ -705,7 +706,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   }
   // ---- operand A: fp32 blocks are read as tf32 in place; bf16 needs a converted copy ----
   const void* At = val;
-  if (bf16) {
+  if (bf16 && !packed) {
     const int64_t elems = nnzb * bs * bs;
     void* sa = scratch(kScratchBsrA, (size_t)elems * 2, st);
     if (sa == nullptr) return SPMMDB_ERR_ALLOC;
@@ -806,6 +807,16 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   if (P == 2) return launch_tc<false, 2>(a, mapB, mapA, grid, smem_bytes, st);
   if (P == 4) return launch_tc<false, 4>(a, mapB, mapA, grid, smem_bytes, st);
   return launch_tc<false, 3>(a, mapB, mapA, grid, smem_bytes, st);
+}
+
+int bsr_pack_bf16(int64_t elems, const float* in, void* out, cudaStream_t st) {
+  const int64_t n4 = elems / 4;
+  if (n4 > 0) {
+    int blocks = (int)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
+    cvt_bf16_kernel<<<blocks, 256, 0, st>>>((const float4*)in, (uint2*)out, n4);
+    SPMMDB_CUDA_OK(cudaGetLastError());
+  }
+  return SPMMDB_OK;
 }
 
 }  // namespace spmmdb

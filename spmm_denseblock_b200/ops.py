@@ -13,7 +13,7 @@ from ._lib import lib, check
 
 ROW_MAJOR, COL_MAJOR = 0, 1
 DIR_ROW, DIR_COLUMN = 0, 1
-MATH_FP32, MATH_TF32, MATH_BF16 = 0, 1, 2
+MATH_FP32, MATH_TF32, MATH_BF16, MATH_BF16_PACKED = 0, 1, 2, 3
 
 
 def _stream():
@@ -200,3 +200,12 @@ def block_metrics(rowptr, colind, block_dim):
     tmp = torch.empty(nb + 1, dtype=torch.int32, device=rowptr.device)
     nnzb = csr2bsr_nnz(n, n, rowptr, colind, block_dim, tmp)
     return nnzb, nnzb / (nb * nb), nnz / (nnzb * block_dim * block_dim), nnz / nnzb
+
+
+def bsr_pack_bf16(bsr_val, block_dim):
+    """bf16 copy of the blocks for bsrmm(..., math=MATH_BF16_PACKED): made once per matrix."""
+    _dev(bsr_val)
+    out = torch.empty(bsr_val.numel(), dtype=torch.bfloat16, device=bsr_val.device)
+    nnzb = bsr_val.numel() // (block_dim * block_dim)
+    check(lib().spmmdb_bsr_pack_bf16(nnzb, block_dim, _p(bsr_val), _p(out), _stream()), "spmmdb_bsr_pack_bf16")
+    return out

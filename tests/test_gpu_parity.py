@@ -378,6 +378,36 @@ def test_csrmm_host_entry_slab_pipeline(pkg, oracle, K, alpha, beta):
     assert np.max(np.abs(hC - ref)) <= 1e-3
 
 
+@pytest.mark.parametrize("bs", [16, 32, 64])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_bsrmm_bf16_packed_blocks(pkg, oracle, bs, direction):
+    """SPMMDB_MATH_BF16_PACKED: blocks converted once by spmmdb_bsr_pack_bf16; same result as the per-call bf16
+    path bit for bit, within the tensor-core tolerance of the fp64 oracle; unsupported shapes are refused."""
+    rng = np.random.default_rng(bs + direction)
+    mb, nb, n = 37, 41, 128
+    rp, ci, v = random_bsr(rng, mb, nb, bs, 6, values="sparse")
+    B = rng.uniform(-1, 1, (nb * bs, n)).astype(np.float32)
+    dv = dev(v)
+    packed = pkg.bsr_pack_bf16(dv, bs)
+    assert packed.dtype == torch.bfloat16 and torch.equal(packed.float(), dv.to(torch.bfloat16).float())
+    outs = []
+    for math, vals in ((pkg.MATH_BF16, dv), (pkg.MATH_BF16_PACKED, packed)):
+        C = torch.full((mb * bs, n), float("nan"), device="cuda")
+        pkg.bsrmm(direction, 1, mb, n, nb, ci.size, 1.0, vals, dev(rp), dev(ci), bs, dev(B), n, 0.0, C, n,
+                  c_layout=pkg.ROW_MAJOR, math=math)
+        outs.append(C)
+    assert torch.equal(outs[0], outs[1])
+    ref = oracle.bsrmm(rp, ci, v, bs, B, n, n, 1, direction=direction, c_layout=0)
+    scale = oracle.bsrmm(rp, ci, np.abs(v), bs, np.abs(B), n, n, 1, direction=direction, c_layout=0)
+    assert np.max(np.abs(outs[1].cpu().numpy() - ref) / np.maximum(scale, 1e-30)) <= TOL_TC
+    # a block size the tensor-core kernel does not take cannot read bf16 blocks
+    L = pkg.lib()
+    z = torch.zeros(64, device="cuda")
+    rc = L.spmmdb_bsrmm_f32(0, 1, 1, 8, 1, 1, 5, 1.0, z.data_ptr(), dev(np.array([0, 1], np.int32)).data_ptr(),
+                            dev(np.array([0], np.int32)).data_ptr(), z.data_ptr(), 8, 0.0, z.data_ptr(), 8, 0, 3, None)
+    assert rc == -2
+
+
 # ----------------------------------------------------------------------------- divide (hybrid split)
 def _banded_graph(rng, n, band=16, p_dense=0.7, avg=4):
     rows = []

@@ -1,4 +1,2 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_gpu.log
-timeout 300 python tools/time_kernels.py --cases c2,c2l,c4csr 2>/dev/null | cut -c1-200
+for seg in 32 64 128 256 512; do echo "seg=$seg"; SPMMDB_CSR_SEG=$seg timeout 300 python tools/time_kernels.py --cases c2,c2l 2>/dev/null | cut -c1-170; done

@@ -65,10 +65,12 @@ def bsr_case(name, rp, ci, val, B, K, bs, maths, flush):
     Bp = torch.zeros(mb * bs, K, device="cuda")
     Bp[:n] = B
     Cb = torch.zeros(mb * bs, K, device="cuda")
+    bv16 = pkg.bsr_pack_bf16(bv, bs) if 3 in maths else None
     for math in maths:
-        med, best = timeit(lambda: pkg.bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 0.0, Cb, K,
+        vals = bv16 if math == 3 else bv
+        med, best = timeit(lambda: pkg.bsrmm(0, 1, mb, K, mb, nnzb, 1.0, vals, brp, bci, bs, Bp, K, 0.0, Cb, K,
                                              c_layout=0, math=math), warmup=2, iters=5, flush=flush)
-        byts = 4 * (mb + 1) + 4 * nnzb + 4 * nnzb * bs * bs + 4 * n * K * 2
+        byts = 4 * (mb + 1) + 4 * nnzb + (2 if math == 3 else 4) * nnzb * bs * bs + 4 * n * K * 2
         print(json.dumps(dict(case=name, kernel="bsrmm", math=math, bs=bs, ms_med=med, ms_min=best,
                               useful_gflops=2 * nnz * K / med / 1e6, dense_tflops=2 * nnzb * bs * bs * K / med / 1e9,
                               gbs=byts / med / 1e6, frac_hbm=byts / med / 1e6 / HBM)), flush=True)
