@@ -40,6 +40,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) csr2bsr_kernel(
   const int wid = threadIdx.x >> 5;
   if (wid >= warps_per_cta) return;
   const int bs2 = bs * bs;
+  const int shift = (bs & (bs - 1)) == 0 ? __ffs(bs) - 1 : -1;  // power-of-two block size: shift instead of divide
   float* tile = smem + (size_t)wid * bs2;
   if (MODE == 1) {
     for (int i = lane; i < bs2; i += 32) tile[i] = 0.f;
@@ -54,7 +55,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) csr2bsr_kernel(
       p[t] = 0; e[t] = 0;
       if (r < bs && row < m) { p[t] = __ldg(rowptr + row); e[t] = __ldg(rowptr + row + 1); }
       col[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) : -1;
-      head[t] = (col[t] >= 0) ? col[t] / bs : INT_MAX;
+      head[t] = (col[t] >= 0) ? (shift >= 0 ? col[t] >> shift : col[t] / bs) : INT_MAX;
     }
     const int64_t base = (MODE == 0) ? 0 : __ldg(bsr_rowptr + ib);
     int step = 0;
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) csr2bsr_kernel(
           }
           ++p[t];
           col[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) : -1;
-          head[t] = (col[t] >= 0) ? col[t] / bs : INT_MAX;
+          head[t] = (col[t] >= 0) ? (shift >= 0 ? col[t] >> shift : col[t] / bs) : INT_MAX;
         }
       }
       if (MODE == 1) {
@@ -250,6 +251,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) divide_kernel(
   const int wid = threadIdx.x >> 5;
   if (wid >= warps_per_cta) return;
   const int bs2 = bs * bs;
+  const int shift = (bs & (bs - 1)) == 0 ? __ffs(bs) - 1 : -1;
   float* tile = smem + (size_t)wid * bs2;
   if (MODE == 1) {
     for (int i = lane; i < bs2; i += 32) tile[i] = 0.f;
@@ -263,7 +265,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) divide_kernel(
       const int row = ib * bs + r;
       p[t] = 0; e[t] = 0;
       if (r < bs && row < m) { p[t] = __ldg(rowptr + row); e[t] = __ldg(rowptr + row + 1); }
-      head[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) / bs : INT_MAX;
+      head[t] = (p[t] < e[t]) ? (shift >= 0 ? __ldg(colind + p[t]) >> shift : __ldg(colind + p[t]) / bs) : INT_MAX;
       rem[t] = (MODE == 1 && r < bs && row < m) ? __ldg(csr_rowptr + row) : 0;  // MODE 1: next output slot
     }
     const int64_t base = (MODE == 0) ? 0 : __ldg(bsr_rowptr + ib);
@@ -329,7 +331,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) divide_kernel(
       for (int t = 0; t < R; ++t) {
         if (head[t] == bmin) {
           p[t] = q[t];
-          head[t] = (p[t] < e[t]) ? __ldg(colind + p[t]) / bs : INT_MAX;
+          head[t] = (p[t] < e[t]) ? (shift >= 0 ? __ldg(colind + p[t]) >> shift : __ldg(colind + p[t]) / bs) : INT_MAX;
         }
       }
     }

@@ -189,8 +189,9 @@ extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colin
   perm_small_kernel<<<nsm * 8, 256, 0, st>>>(n, rowptr, colind, val, old2new, new_rowptr, new_colind, new_val);
   SPMMDB_CUDA_OK(cudaGetLastError());
   if (h[0] > 0) {
-    const int grid = h[0] < nsm * 16 ? h[0] : nsm * 16;
-    perm_cta_kernel<<<grid, 256, kMediumRow * 8, st>>>(list_m, counters + 0, kMediumRow, rowptr, colind, val, old2new,
+    const int grid = h[0] < nsm * 24 ? h[0] : nsm * 24;
+    // 64-thread CTAs: these rows have 33..1024 entries, and four times as many of them are resident per SM
+    perm_cta_kernel<<<grid, 64, kMediumRow * 8, st>>>(list_m, counters + 0, kMediumRow, rowptr, colind, val, old2new,
                                                       new_rowptr, new_colind, new_val, nullptr);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
