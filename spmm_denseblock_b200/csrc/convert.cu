@@ -13,6 +13,7 @@
 // it out once, fully coalesced (zeros included), so bsr_val is written exactly
 // once and never pre-cleared.
 #include <limits.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -420,6 +421,59 @@ int launch_csr2bsr(int dir, int m, int mb, int bs, const int* rowptr, const int*
 
 }  // namespace
 
+// convert_br.cu: one CTA per block row (coalesced reads, shared-memory bitmap ranks)
+bool convert_br_ok(int n, int bs, bool split);
+int csr2bsr_br(bool fill, int dir, int m, int n, const int* rowptr, const int* colind, const float* val, int bs,
+               int* counts, const int* bsr_rowptr, int* bsr_colind, float* bsr_val, cudaStream_t st);
+int divide_br(bool fill, int dir, int m, int n, const int* rowptr, const int* colind, const float* val, int bs, int thr,
+              int* bsr_counts, int* csr_counts, const int* bsr_rowptr, int* bsr_colind, float* bsr_val,
+              const int* csr_rowptr, int* csr_colind, float* csr_val, cudaStream_t st);
+// Which path: the block-row kernels win when a block row holds enough entries to keep a CTA busy (C3: 4-9 K entries
+// per block row, csr2bsr 1.64 -> 0.70 ms, split 2.0-4.6 -> 0.5-0.9 ms) and lose on tiny block rows (C4: 34 entries,
+// 0.15 -> 0.41 ms); with blocks under ~8 % fill the fill pass is bound by writing zeros and the warp-merge kernel's
+// full-line tile stores are the faster way (C3 at 3 % fill: 1.57 vs 1.85 ms).  Phase 1 reads nnz = rowptr[m] back
+// (it synchronises anyway) and leaves it, with nnzb, for phase 2 in a small cache keyed by (rowptr, m, block size).
+// SPMMDB_CONVERT_BR = 0 / 1 forces the warp-merge / block-row kernels (read per call: the tests exercise both).
+struct ConvNote { const int* rowptr; int m, bs, dev; int64_t nnz, nnzb; };
+static ConvNote g_conv_notes[8];
+static int g_conv_next = 0;
+static void conv_note(const int* rowptr, int m, int bs, int64_t nnz, int64_t nnzb) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  for (auto& e : g_conv_notes)
+    if (e.rowptr == rowptr && e.m == m && e.bs == bs && e.dev == dev) { e.nnz = nnz; e.nnzb = nnzb; return; }
+  g_conv_notes[g_conv_next] = ConvNote{rowptr, m, bs, dev, nnz, nnzb};
+  g_conv_next = (g_conv_next + 1) % 8;
+}
+static bool conv_lookup(const int* rowptr, int m, int bs, int64_t* nnz, int64_t* nnzb) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  for (auto& e : g_conv_notes)
+    if (e.rowptr == rowptr && e.rowptr != nullptr && e.m == m && e.bs == bs && e.dev == dev) {
+      *nnz = e.nnz; *nnzb = e.nnzb;
+      return true;
+    }
+  return false;
+}
+// nnz < 0: unknown.  nnzb < 0: unknown / not relevant (count passes, split).
+static bool use_br(int m, int n, int bs, bool split, int64_t nnz, int64_t nnzb) {
+  if (!convert_br_ok(n, bs, split)) return false;
+  const char* e = getenv("SPMMDB_CONVERT_BR");
+  if (e != nullptr && e[0] == '0') return false;
+  if (e != nullptr && e[0] == '1') return true;
+  const int64_t mb = ((int64_t)m + bs - 1) / bs;
+  if (nnz >= 0 && mb > 0 && nnz / mb < 512) return false;
+  if (nnz >= 0 && nnzb > 0 && (double)nnz < 0.08 * (double)nnzb * bs * bs) return false;
+  return true;
+}
+static int read_nnz(const int* rowptr, int m, cudaStream_t st, int64_t* nnz) {
+  int h = 0;
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(&h, rowptr + m, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  *nnz = h;
+  return SPMMDB_OK;
+}
+
 int exclusive_scan_i32(const int* counts, int n, int* sums, int* out, cudaStream_t st) {
   return exclusive_scan(counts, n, sums, out, st);
 }
@@ -446,8 +500,14 @@ extern "C" int spmmdb_csr2bsr_nnz(int m, int n, const int* rowptr, const int* co
   if (ws == nullptr) return SPMMDB_ERR_ALLOC;
   int* counts = ws;
   int* sums = ws + mb;
-  int rc = launch_csr2bsr<0>(SPMMDB_DIR_ROW, m, mb, block_dim, rowptr, colind, nullptr, counts, nullptr, nullptr,
-                             nullptr, st);
+  int64_t nnz = -1;
+  int rc = read_nnz(rowptr, m, st, &nnz);
+  if (rc != SPMMDB_OK) return rc;
+  rc = use_br(m, n, block_dim, false, nnz, -1)
+               ? csr2bsr_br(false, SPMMDB_DIR_ROW, m, n, rowptr, colind, nullptr, block_dim, counts, nullptr, nullptr,
+                            nullptr, st)
+               : launch_csr2bsr<0>(SPMMDB_DIR_ROW, m, mb, block_dim, rowptr, colind, nullptr, counts, nullptr, nullptr,
+                                   nullptr, st);
   if (rc != SPMMDB_OK) return rc;
   scan_tile_sums<<<ntiles, 256, 0, st>>>(counts, mb, sums);
   scan_sums_inplace<<<1, 256, 0, st>>>(sums, ntiles);
@@ -455,6 +515,7 @@ extern "C" int spmmdb_csr2bsr_nnz(int m, int n, const int* rowptr, const int* co
   SPMMDB_CUDA_OK(cudaGetLastError());
   SPMMDB_CUDA_OK(cudaMemcpyAsync(nnzb_host, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  conv_note(rowptr, m, block_dim, nnz, *nnzb_host);
   return SPMMDB_OK;
 }
 
@@ -468,13 +529,17 @@ extern "C" int spmmdb_csr2bsr_f32(int dir, int m, int n, const int* rowptr, cons
   if (mb == 0) return SPMMDB_OK;
   if (rowptr == nullptr || bsr_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;  // others may be null when nnz == 0
   cudaStream_t st = (cudaStream_t)stream;
+  int64_t nnz = -1, nnzb = -1;
+  conv_lookup(rowptr, m, block_dim, &nnz, &nnzb);
+  if (use_br(m, n, block_dim, false, nnz, nnzb) && bsr_colind != nullptr && bsr_val != nullptr && val != nullptr)
+    return csr2bsr_br(true, dir, m, n, rowptr, colind, val, block_dim, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);
   if (block_dim <= 128)
     return launch_csr2bsr<1>(dir, m, mb, block_dim, rowptr, colind, val, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);
   // very large blocks: clear + scatter (needs nnzb: read it back)
-  int nnzb = 0;
-  SPMMDB_CUDA_OK(cudaMemcpyAsync(&nnzb, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
+  int nnzb_big = 0;
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(&nnzb_big, bsr_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
-  SPMMDB_CUDA_OK(cudaMemsetAsync(bsr_val, 0, sizeof(float) * (size_t)nnzb * block_dim * block_dim, st));
+  SPMMDB_CUDA_OK(cudaMemsetAsync(bsr_val, 0, sizeof(float) * (size_t)nnzb_big * block_dim * block_dim, st));
   return launch_csr2bsr<2>(dir, m, mb, block_dim, rowptr, colind, val, nullptr, bsr_rowptr, bsr_colind, bsr_val, st);
 }
 
@@ -533,8 +598,15 @@ extern "C" int spmmdb_divide_nnz(int m, int n, const int* rowptr, const int* col
   int* csr_counts = ws + mb;
   int* sums = ws + mb + m;
   const int thr = spmmdb_divide_threshold(block_dim, density);
-  int rc = launch_divide<0>(SPMMDB_DIR_ROW, m, mb, block_dim, thr, rowptr, colind, nullptr, bsr_counts, csr_counts,
-                            nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st);
+  int64_t nnz = -1;
+  int rc = read_nnz(rowptr, m, st, &nnz);
+  if (rc != SPMMDB_OK) return rc;
+  conv_note(rowptr, m, -block_dim, nnz, -1);  // negative block size: the split's own note
+  rc = use_br(m, n, block_dim, true, nnz, -1)
+               ? divide_br(false, SPMMDB_DIR_ROW, m, n, rowptr, colind, nullptr, block_dim, thr, bsr_counts, csr_counts,
+                           nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st)
+               : launch_divide<0>(SPMMDB_DIR_ROW, m, mb, block_dim, thr, rowptr, colind, nullptr, bsr_counts,
+                                  csr_counts, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st);
   if (rc != SPMMDB_OK) return rc;
   if ((rc = exclusive_scan(bsr_counts, mb, sums, bsr_rowptr, st)) != SPMMDB_OK) return rc;
   if ((rc = exclusive_scan(csr_counts, m, sums, csr_rowptr, st)) != SPMMDB_OK) return rc;
@@ -555,6 +627,11 @@ extern "C" int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const
   if (mb == 0) return SPMMDB_OK;
   if (rowptr == nullptr || bsr_rowptr == nullptr || csr_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
   const int thr = spmmdb_divide_threshold(block_dim, density);
+  int64_t nnz = -1, nnzb = -1;
+  conv_lookup(rowptr, m, -block_dim, &nnz, &nnzb);
+  if (use_br(m, n, block_dim, true, nnz, -1))
+    return divide_br(true, dir, m, n, rowptr, colind, val, block_dim, thr, nullptr, nullptr, bsr_rowptr, bsr_colind,
+                     bsr_val, csr_rowptr, csr_colind, csr_val, (cudaStream_t)stream);
   return launch_divide<1>(dir, m, mb, block_dim, thr, rowptr, colind, val, nullptr, nullptr, bsr_rowptr, bsr_colind,
                           bsr_val, csr_rowptr, csr_colind, csr_val, (cudaStream_t)stream);
 }

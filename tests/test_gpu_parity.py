@@ -30,6 +30,24 @@ def dev(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
 
+@pytest.fixture(autouse=True, params=["block_row", "warp_merge"])
+def conversion_path(request, monkeypatch):
+    """csr2bsr and the hybrid split have two device paths with identical outputs (one CTA per block row with
+    shared-memory bitmap ranks; one warp per block row merging the rows, which also serves shapes whose bitmap
+    does not fit shared memory).  Every test that converts runs on both."""
+    name = request.node.name
+    converts = any(k in name for k in ("csr2bsr", "divide", "conversion", "round_trip", "roundtrip", "check_result",
+                                       "metrics"))
+    if request.param == "warp_merge":
+        if not converts:
+            pytest.skip("no conversion in this test")
+        monkeypatch.setenv("SPMMDB_CONVERT_BR", "0")
+    elif converts:
+        monkeypatch.setenv("SPMMDB_CONVERT_BR", "1")  # else small inputs would all pick the warp-merge path
+    else:
+        monkeypatch.delenv("SPMMDB_CONVERT_BR", raising=False)
+
+
 def err_vs(oracle, got, ref64, rp, ci, v, Bm, K, **kw):
     scale = oracle.csrmm(rp, ci, np.abs(v), np.abs(Bm), K, **kw)
     return float(np.max(np.abs(got.astype(np.float64) - ref64) / np.maximum(scale, 1e-30)))
