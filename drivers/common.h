@@ -92,22 +92,21 @@ struct HostCsr {
 };
 
 // tmp/<graph>_indptr.txt = "<n+1>\n" then n+1 ints; tmp/<graph>_indices.txt = "<nnz>\n" then nnz ints
-// (what dumpCSRToFile writes and loadCSRFromFile reads, load_data.cc:125-165)
-inline std::vector<int> read_int_file(const std::string& path) {
-  std::ifstream f(path);
-  if (!f) throw std::runtime_error("cannot open " + path);
-  long long cnt = 0;
-  f >> cnt;
-  std::vector<int> v((size_t)cnt);
-  for (auto& x : v) f >> x;
-  if (!f) throw std::runtime_error("short read in " + path);
-  return v;
-}
+// (what dumpCSRToFile writes and loadCSRFromFile reads, load_data.cc:125-165), or tmp/<graph>.csrbin when a
+// binary copy exists (drivers/graph2bin makes one): the library's multi-threaded readers, not ifstream >>.
 inline HostCsr load_csr_text(const std::string& prefix, float fill = 1.0f) {
   HostCsr a;
-  a.rowptr = read_int_file(prefix + "_indptr.txt");
-  a.colind = read_int_file(prefix + "_indices.txt");
-  a.m = a.n = (int)a.rowptr.size() - 1;
+  int n = 0;
+  int64_t nnz = 0;
+  int *rp = nullptr, *ci = nullptr;
+  int rc = spmmdb_graph_read(prefix.c_str(), SPMMDB_GRAPH_AUTO, &n, &nnz, &rp, &ci);
+  if (rc == SPMMDB_ERR_IO) throw std::runtime_error("cannot open or short read in " + prefix + "_indptr.txt / _indices.txt");
+  if (rc != SPMMDB_OK) throw std::runtime_error("malformed graph files " + prefix);
+  a.rowptr.assign(rp, rp + n + 1);
+  a.colind.assign(ci, ci + nnz);
+  spmmdb_graph_free(rp);
+  spmmdb_graph_free(ci);
+  a.m = a.n = n;
   a.val.assign(a.colind.size(), fill);  // unit adjacency weights (run_csrmm.cu:66)
   return a;
 }

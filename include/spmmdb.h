@@ -37,7 +37,8 @@ typedef enum {
   SPMMDB_ERR_NOT_SUPPORTED = -2,  /* cusparse: CUSPARSE_STATUS_MATRIX_TYPE_NOT_SUPPORTED */
   SPMMDB_ERR_CUDA = -3,           /* a CUDA runtime call failed (see spmmdb_last_error)  */
   SPMMDB_ERR_ALLOC = -4,          /* internal workspace allocation failed                */
-  SPMMDB_ERR_ARCH = -5            /* device is not sm_100 (tcgen05 path requested)       */
+  SPMMDB_ERR_ARCH = -5,           /* device is not sm_100 (tcgen05 path requested)       */
+  SPMMDB_ERR_IO = -6              /* graph file missing, short or malformed              */
 } spmmdb_status;
 
 #define SPMMDB_ROW_MAJOR 0
@@ -221,6 +222,30 @@ int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr,
  * bit-identical to the single-GPU result.
  * ------------------------------------------------------------------------ */
 int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds);
+
+/* --------------------------------------------------------------------------
+ * Graph files.  HOST functions, no CUDA call.
+ *   SPMMDB_GRAPH_TEXT      <path>_indptr.txt + <path>_indices.txt, the reference's cache format
+ *                          (dumpCSRToFile / loadCSRFromFile, load_data.cc:125-165): read, and written
+ *                          byte for byte as the reference writes it
+ *   SPMMDB_GRAPH_EDGELIST  <path> = "<n> <nnz>" then nnz pairs "x y" (loadGraphFromFile
+ *                          load_data.cc:167-184 + convertGraphToCSR utility.cc:31-45: neighbour lists
+ *                          sorted ascending, duplicate edges kept, nnz taken from the header); read only
+ *   SPMMDB_GRAPH_BINARY    <path>.csrbin: 32-byte header {"SPMMDBG1", int64 rows, int64 cols, int64 nnz},
+ *                          int32 rowptr[rows+1], int32 colind[nnz] (little endian)
+ *   SPMMDB_GRAPH_AUTO      read only: the binary file if <path>.csrbin exists, else the text pair
+ * spmmdb_graph_read returns malloc'ed arrays (release each with spmmdb_graph_free); the text
+ * parsers run on all host cores (SPMMDB_IO_THREADS overrides).  Where the reference reads garbage
+ * from a missing or short file, these return SPMMDB_ERR_IO.
+ * ------------------------------------------------------------------------ */
+#define SPMMDB_GRAPH_TEXT 0
+#define SPMMDB_GRAPH_BINARY 1
+#define SPMMDB_GRAPH_EDGELIST 2
+#define SPMMDB_GRAPH_AUTO 3
+int spmmdb_graph_read(const char* path, int format, int* n, int64_t* nnz, int** rowptr, int** colind);
+int spmmdb_graph_write(const char* prefix, int format, int n, int64_t nnz, const int* rowptr,
+                       const int* colind);
+void spmmdb_graph_free(void* p);
 
 #ifdef __cplusplus
 }

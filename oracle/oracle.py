@@ -321,3 +321,58 @@ def ref_divide_matrix(rowptr, colind, bs, density):
     f(n, rowptr, colind, bs, density, crp.ctypes.data, cci.ctypes.data, brp.ctypes.data, bci.ctypes.data,
       bv.ctypes.data, C.byref(cnnz))
     return crp, cci[:cnnz.value], brp, bci[:nnzb], bv[:nnzb * bs * bs].reshape(nnzb, bs, bs)
+
+
+# ---- graph files (load_data.cc:125-184), numpy restatement + the reference's own loaders ------------------
+def dump_csr_text(prefix, rowptr, colind):
+    """dumpCSRToFile (load_data.cc:125-141): "<count>\\n", every value followed by a space, "\\n"."""
+    for name, a in (("_indptr.txt", rowptr), ("_indices.txt", colind)):
+        with open(prefix + name, "w") as f:
+            f.write(f"{len(a)}\n" + "".join(f"{int(x)} " for x in a) + "\n")
+
+
+def load_csr_text(prefix):
+    """loadCSRFromFile (load_data.cc:143-165): the first <count> integers after the count."""
+    out = []
+    for name in ("_indptr.txt", "_indices.txt"):
+        tok = open(prefix + name).read().split()
+        cnt = int(tok[0])
+        out.append(np.array(tok[1:1 + cnt], dtype=np.int64).astype(np.int32))
+    return out[0], out[1]
+
+
+def load_edge_list_csr(path):
+    """loadGraphFromFile (load_data.cc:167-184: push_back per pair, std::sort per row, duplicates kept,
+    nnz from the header) + convertGraphToCSR (utility.cc:31-45)."""
+    tok = open(path).read().split()
+    n, nnz = int(tok[0]), int(tok[1])
+    adj = [[] for _ in range(n)]
+    for e in range(nnz):
+        adj[int(tok[2 + 2 * e])].append(int(tok[3 + 2 * e]))
+    rowptr = np.zeros(n + 1, np.int32)
+    rowptr[1:] = np.cumsum([len(a) for a in adj])
+    colind = np.array([c for a in adj for c in sorted(a)], np.int32)
+    return rowptr, colind
+
+
+def ref_load_csr(prefix, cap_rows, cap_nnz):
+    L = ref_host_lib()
+    L.ref_load_csr.argtypes = [C.c_char_p, _i32p, C.c_int, _i32p, C.c_int, C.POINTER(C.c_int)]
+    rp, ci, nnz = np.zeros(cap_rows, np.int32), np.zeros(max(cap_nnz, 1), np.int32), C.c_int(0)
+    n = L.ref_load_csr(prefix.encode(), rp, cap_rows, ci, cap_nnz, C.byref(nnz))
+    return rp[:n + 1], ci[:nnz.value]
+
+
+def ref_load_graph_csr(path, cap_rows, cap_nnz):
+    L = ref_host_lib()
+    L.ref_load_graph_csr.argtypes = [C.c_char_p, _i32p, C.c_int, _i32p, C.c_int, C.POINTER(C.c_int)]
+    rp, ci, nnz = np.zeros(cap_rows, np.int32), np.zeros(max(cap_nnz, 1), np.int32), C.c_int(0)
+    n = L.ref_load_graph_csr(path.encode(), rp, cap_rows, ci, cap_nnz, C.byref(nnz))
+    return rp[:n + 1], ci[:nnz.value]
+
+
+def ref_dump_csr(prefix, rowptr, colind):
+    L = ref_host_lib()
+    L.ref_dump_csr.argtypes = [C.c_char_p, C.c_int, C.c_int, _i32p, _i32p]
+    L.ref_dump_csr(prefix.encode(), len(rowptr) - 1, len(colind), np.ascontiguousarray(rowptr, np.int32),
+                   np.ascontiguousarray(colind if len(colind) else np.zeros(1), np.int32))

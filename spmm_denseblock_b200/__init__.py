@@ -13,3 +13,6 @@ from .ops import (  # noqa: F401
     gespmm_csrmm, csrmm, bsrmm, rocsparse_bsrmm, block_gemm, csr2bsr_nnz, csr2bsr, bsr2csr,
     csrmm_segment, set_csrmm_segment, divide, divide_threshold, permute_csr, permute_rows, heatmap, block_metrics,
 )
+from .graphio import (  # noqa: F401
+    GRAPH_TEXT, GRAPH_BINARY, GRAPH_EDGELIST, GRAPH_AUTO, read_graph, write_graph,
+)

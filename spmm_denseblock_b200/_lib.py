@@ -14,7 +14,7 @@ class SpmmdbError(RuntimeError):
     pass
 
 
-STATUS = {0: "OK", -1: "INVALID_VALUE", -2: "NOT_SUPPORTED", -3: "CUDA", -4: "ALLOC", -5: "ARCH"}
+STATUS = {0: "OK", -1: "INVALID_VALUE", -2: "NOT_SUPPORTED", -3: "CUDA", -4: "ALLOC", -5: "ARCH", -6: "IO"}
 
 # name -> argtypes; every symbol include/spmmdb.h declares
 SIGNATURES = {
@@ -42,6 +42,9 @@ SIGNATURES = {
     "spmmdb_set_bsrmm_math": [C.c_int],
     "spmmdb_get_bsrmm_math": [],
     "spmmdb_shard_plan": [vp, C.c_int, C.c_int, C.c_int, vp],
+    "spmmdb_graph_read": [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(c_i64), C.POINTER(vp), C.POINTER(vp)],
+    "spmmdb_graph_write": [C.c_char_p, C.c_int, C.c_int, c_i64, vp, vp],
+    "spmmdb_graph_free": [vp],
     "spmmdb_version": [],
     "spmmdb_last_error": [],
     "spmmdb_device_sm": [],
@@ -67,6 +70,7 @@ def lib():
             fn.restype = C.c_int
         L.spmmdb_version.restype = C.c_char_p
         L.spmmdb_last_error.restype = C.c_char_p
+        L.spmmdb_graph_free.restype = None
         _LIB = L
     return _LIB
 

@@ -9,7 +9,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "drivers", "bin")
-PROGS = ["run_csrmm", "run_bsrmm", "test_csrmm", "test_bsrmm", "check_result", "csr2bsr", "bsr2csr", "block_cublas", "divide"]
+PROGS = ["run_csrmm", "run_bsrmm", "test_csrmm", "test_bsrmm", "check_result", "csr2bsr", "bsr2csr", "block_cublas", "divide", "graph2bin"]
 
 
 def _build():
