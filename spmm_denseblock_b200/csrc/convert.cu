@@ -177,6 +177,90 @@ __global__ void __launch_bounds__(256) scan_apply(const int* __restrict__ in, in
 }
 
 // ---- bsr2csr ------------------------------------------------------------------
+// Closed form of cusparseSbsr2csr (every slot of every block becomes a CSR entry, explicit zeros included):
+// block p of block row ib (q-th of its cnt blocks) puts row r of the block at b0*bs^2 + r*cnt*bs + q*bs.
+//
+// bsr2csr_vec_kernel (bs a multiple of 4 that divides evenly into float4 pieces, row-major blocks, 16-byte
+// aligned arrays): a warp owns a run of CH consecutive blocks, finds the block row of the first one with a
+// single binary search and walks bsr_rowptr from there; every block is read as float4s (U blocks in flight
+// per lane) and each float4 goes out with its int4 of column ids.  bsr2csr_kernel below is the scalar
+// any-size / column-major path (one warp per block).
+template <int BS, int U>
+__global__ void __launch_bounds__(256) bsr2csr_vec_kernel(int mb, const int* __restrict__ bsr_rowptr,
+                                                          const int* __restrict__ bsr_colind,
+                                                          const float* __restrict__ bsr_val,
+                                                          int* __restrict__ csr_rowptr, int* __restrict__ csr_colind,
+                                                          float* __restrict__ csr_val, int ch) {
+  constexpr int BS2 = BS * BS;
+  constexpr int Q = BS / 4;                       // float4 pieces per block row
+  constexpr int PIECES = BS2 / 4;                 // per block
+  constexpr int V = (PIECES + 31) / 32;           // per lane per block
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int nnzb = __ldg(bsr_rowptr + mb);
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row <= (int64_t)mb * BS;
+       row += (int64_t)gridDim.x * blockDim.x) {
+    if (row == (int64_t)mb * BS) { csr_rowptr[row] = nnzb * BS2; break; }
+    const int ib = (int)(row / BS), r = (int)(row % BS);
+    const int b0 = __ldg(bsr_rowptr + ib), cnt = __ldg(bsr_rowptr + ib + 1) - b0;
+    csr_rowptr[row] = b0 * BS2 + r * cnt * BS;
+  }
+  const int64_t nchunks = ((int64_t)nnzb + ch - 1) / ch;
+  for (int64_t chunk = warp; chunk < nchunks; chunk += nwarps) {
+    const int p0 = (int)(chunk * ch), p1 = min(nnzb, p0 + ch);
+    int ib = 0;
+    if (lane == 0) {
+      int lo = 0, hi = mb;  // largest ib with bsr_rowptr[ib] <= p0
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(bsr_rowptr + mid) <= p0) lo = mid; else hi = mid;
+      }
+      ib = lo;
+    }
+    ib = __shfl_sync(0xffffffffu, ib, 0);
+    int row_end = __ldg(bsr_rowptr + ib + 1);
+    for (int p = p0; p < p1; p += U) {
+      float4 v[U][V];
+      int64_t out0[U], stride[U];
+      int col0[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int pp = p + u;
+        if (pp < p1) {
+          while (pp >= row_end) row_end = __ldg(bsr_rowptr + (++ib) + 1);  // skips empty block rows
+          const int64_t b0 = __ldg(bsr_rowptr + ib);
+          stride[u] = (int64_t)(row_end - b0) * BS;
+          out0[u] = b0 * BS2 + (int64_t)(pp - b0) * BS;
+          col0[u] = __ldg(bsr_colind + pp) * BS;
+          const float4* __restrict__ blk = reinterpret_cast<const float4*>(bsr_val + (int64_t)pp * BS2);
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            const int f = lane + 32 * j;
+            if (PIECES % 32 == 0 || f < PIECES) v[u][j] = __ldcs(blk + f);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (p + u < p1) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            const int f = lane + 32 * j;
+            if (PIECES % 32 == 0 || f < PIECES) {
+              const int r = f / Q, c = (f % Q) * 4;
+              const int64_t o = out0[u] + r * stride[u] + c;
+              const int cc = col0[u] + c;
+              __stcs(reinterpret_cast<int4*>(csr_colind + o), make_int4(cc, cc + 1, cc + 2, cc + 3));
+              __stcs(reinterpret_cast<float4*>(csr_val + o), v[u][j]);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 // One warp per non-zero block.  Lane 0 finds the block row with a binary search
 // over bsr_rowptr; the warp then reads the block contiguously and writes each of
 // its bs row pieces to its closed-form position.
@@ -552,8 +636,24 @@ extern "C" int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr
   if (device_sm() < 0) return SPMMDB_ERR_CUDA;
   cudaStream_t st = (cudaStream_t)stream;
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
-  bsr2csr_kernel<<<nsm * 8, 256, 0, st>>>(dir, mb, block_dim, bsr_rowptr, bsr_colind, bsr_val, csr_rowptr,
-                                          csr_colind, csr_val);
+  const bool aligned = ((((uintptr_t)bsr_val) | ((uintptr_t)csr_val) | ((uintptr_t)csr_colind)) & 15) == 0;
+  static const int force_scalar = getenv("SPMMDB_BSR2CSR_SCALAR") ? atoi(getenv("SPMMDB_BSR2CSR_SCALAR")) : 0;
+  if (dir == SPMMDB_DIR_ROW && aligned && !force_scalar &&
+      (block_dim == 8 || block_dim == 16 || block_dim == 32 || block_dim == 64)) {
+    // a warp's run of blocks: ~16 KB of block values, so the one binary search per run is noise
+    const int ch = max(1, 4096 / (block_dim * block_dim));
+    const int grid = nsm * 8;
+#define SPMMDB_B2C(BS, U) \
+  bsr2csr_vec_kernel<BS, U><<<grid, 256, 0, st>>>(mb, bsr_rowptr, bsr_colind, bsr_val, csr_rowptr, csr_colind, csr_val, ch)
+    if (block_dim == 8) SPMMDB_B2C(8, 8);
+    else if (block_dim == 16) SPMMDB_B2C(16, 4);
+    else if (block_dim == 32) SPMMDB_B2C(32, 1);
+    else SPMMDB_B2C(64, 1);
+#undef SPMMDB_B2C
+  } else {
+    bsr2csr_kernel<<<nsm * 8, 256, 0, st>>>(dir, mb, block_dim, bsr_rowptr, bsr_colind, bsr_val, csr_rowptr,
+                                            csr_colind, csr_val);
+  }
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
 }

@@ -176,7 +176,7 @@ def test_csr2bsr_bit_exact(pkg, oracle, bs, direction):
     assert np.array_equal(bv.cpu().numpy().view(np.uint32), ov.ravel().view(np.uint32))
 
 
-@pytest.mark.parametrize("bs", [2, 5, 16, 32, 64])
+@pytest.mark.parametrize("bs", [2, 5, 8, 16, 32, 64])
 @pytest.mark.parametrize("direction", [0, 1])
 def test_bsr2csr_bit_exact(pkg, oracle, bs, direction):
     rng = np.random.default_rng(bs + 100 * direction)
@@ -185,6 +185,26 @@ def test_bsr2csr_bit_exact(pkg, oracle, bs, direction):
     crp, cci, cv = pkg.bsr2csr(mb, nb, dev(brp), dev(bci), dev(bv), bs, direction=direction)
     orp, oci, ov = oracle.bsr2csr(brp, bci, bv, bs, direction=direction)
     assert np.array_equal(crp.cpu().numpy(), orp)
+    assert np.array_equal(cci.cpu().numpy(), oci)
+    assert np.array_equal(cv.cpu().numpy().view(np.uint32), ov.view(np.uint32))
+
+
+@pytest.mark.parametrize("bs", [8, 16, 32])
+def test_bsr2csr_block_runs_cross_empty_block_rows_and_unaligned_input(pkg, oracle, bs):
+    """The float4 path walks bsr_rowptr along a warp's run of blocks: mostly-empty block rows, runs that span
+    many block rows, and a bsr_val that is not 16-byte aligned (scalar path) all give the closed form."""
+    rng = np.random.default_rng(40 + bs)
+    mb, nb = 2500, 300
+    brp, bci, bv = random_bsr(rng, mb, nb, bs, 0.6, values="sparse")
+    assert (np.diff(brp) == 0).sum() > mb // 3
+    orp, oci, ov = oracle.bsr2csr(brp, bci, bv, bs)
+    crp, cci, cv = pkg.bsr2csr(mb, nb, dev(brp), dev(bci), dev(bv), bs)
+    assert np.array_equal(crp.cpu().numpy(), orp) and np.array_equal(cci.cpu().numpy(), oci)
+    assert np.array_equal(cv.cpu().numpy().view(np.uint32), ov.view(np.uint32))
+    shifted = torch.empty(bv.size + 1, device="cuda")[1:]
+    shifted.copy_(torch.from_numpy(bv.ravel()))
+    assert shifted.data_ptr() % 16 != 0
+    crp, cci, cv = pkg.bsr2csr(mb, nb, dev(brp), dev(bci), shifted, bs)
     assert np.array_equal(cci.cpu().numpy(), oci)
     assert np.array_equal(cv.cpu().numpy().view(np.uint32), ov.view(np.uint32))
 
