@@ -76,9 +76,12 @@ template <> struct VecOps<float> {
 // lanes of the warp (shuffles); groups whose range is empty idle.
 // nvec = number of V-vectors per row of B that this column tile covers,
 // vbase = first vector index of the tile.
-template <typename V, int LPR, int VEC, int U, typename Args>
-__device__ __forceinline__ void accumulate_segment(const Args& a, int lb, int hb, int sub, int grp,
-                                                   int vbase, int nvec, V (&acc)[VEC]) {
+// `c`, `v` hold the group's first chunk (entry lb + sub, or 0 past hb).  PF: the next chunk is loaded before
+// the current one is consumed, so only the first chunk of a row is on the latency chain (two more live
+// registers: used where rows / segments span several chunks).
+template <typename V, int LPR, int VEC, int U, bool PF, typename Args>
+__device__ __forceinline__ void accumulate_preloaded(const Args& a, int lb, int hb, int sub, int grp,
+                                                     int vbase, int nvec, V (&acc)[VEC], int c, float v) {
   using Ops = VecOps<V>;
   const V* __restrict__ Bv = reinterpret_cast<const V*>(a.B);
   const int64_t ldbv = a.ldb / Ops::W;
@@ -87,12 +90,12 @@ __device__ __forceinline__ void accumulate_segment(const Args& a, int lb, int hb
   for (int i = 0; i < VEC; ++i) colok[i] = (sub + i * LPR) < nvec;
 
   for (int base = lb; __any_sync(0xffffffffu, base < hb); base += LPR) {
-    const int idx = base + sub;
-    int c = 0;
-    float v = 0.f;
-    if (idx < hb) {
-      c = __ldg(a.colind + idx);
-      v = __ldg(a.val + idx);
+    const int nidx = base + LPR + sub;
+    int cn = 0;
+    float vn = 0.f;
+    if (PF && nidx < hb) {
+      cn = __ldg(a.colind + nidx);
+      vn = __ldg(a.val + nidx);
     }
     const int cnt = hb - base;  // entries of this group's chunk (may be <= 0 or > LPR)
 #pragma unroll 1
@@ -121,7 +124,26 @@ __device__ __forceinline__ void accumulate_segment(const Args& a, int lb, int hb
         }
       }
     }
+    if (PF) {
+      c = cn;
+      v = vn;
+    } else if (nidx < hb) {
+      c = __ldg(a.colind + nidx);
+      v = __ldg(a.val + nidx);
+    }
   }
+}
+
+template <typename V, int LPR, int VEC, int U, bool PF = false, typename Args>
+__device__ __forceinline__ void accumulate_segment(const Args& a, int lb, int hb, int sub, int grp,
+                                                   int vbase, int nvec, V (&acc)[VEC]) {
+  int c = 0;
+  float v = 0.f;
+  if (lb + sub < hb) {
+    c = __ldg(a.colind + lb + sub);
+    v = __ldg(a.val + lb + sub);
+  }
+  accumulate_preloaded<V, LPR, VEC, U, PF>(a, lb, hb, sub, grp, vbase, nvec, acc, c, v);
 }
 
 template <typename V, int LPR, int VEC, typename Args>
@@ -193,8 +215,132 @@ __global__ void __launch_bounds__(256) csrmm_rows_kernel(const CsrArgs a) {
   }
 }
 
+// Rows kernel for small short-row matrices whose dense width fits one column tile (K <= 4 * LPR * VEC):
+// persistent groups walk rows gid, gid + G, gid + 2G, ... and load the NEXT row's first chunk of
+// (column, value) pairs and the row pointers of the row after it before gathering for the current
+// row, so the rowptr -> colind -> B chain of a row overlaps the gathers of the row before it.  Same
+// arithmetic per row as csrmm_rows_kernel (bit-identical output), same long-row queue.
+template <typename V, int LPR, int VEC, int U>
+__global__ void __launch_bounds__(256, 3) csrmm_rows_pipe_kernel(const CsrArgs a) {
+  constexpr int GPW = 32 / LPR;
+  using Ops = VecOps<V>;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane % LPR, grp = lane / LPR;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t G = (((int64_t)gridDim.x * blockDim.x) >> 5) * GPW;
+  const int nvec = (a.K + Ops::W - 1) / Ops::W;
+
+  int64_t row = warp * GPW + grp;
+  int lb = 0, hb = 0;
+  if (row < a.m) {
+    lb = __ldg(a.rowptr + row);
+    hb = __ldg(a.rowptr + row + 1);
+  }
+  int c = 0;
+  float v = 0.f;
+  if (lb + sub < hb && hb - lb <= a.seg) {
+    c = __ldg(a.colind + lb + sub);
+    v = __ldg(a.val + lb + sub);
+  }
+  int nlb = 0, nhb = 0;
+  if (row + G < a.m) {
+    nlb = __ldg(a.rowptr + row + G);
+    nhb = __ldg(a.rowptr + row + G + 1);
+  }
+  while (__any_sync(0xffffffffu, row < a.m)) {
+    int cn = 0;
+    float vn = 0.f;
+    if (nlb + sub < nhb && nhb - nlb <= a.seg) {
+      cn = __ldg(a.colind + nlb + sub);
+      vn = __ldg(a.val + nlb + sub);
+    }
+    int nnlb = 0, nnhb = 0;
+    if (row + 2 * G < a.m) {
+      nnlb = __ldg(a.rowptr + row + 2 * G);
+      nnhb = __ldg(a.rowptr + row + 2 * G + 1);
+    }
+    const bool valid = row < a.m;
+    const bool is_long = (hb - lb) > a.seg;
+    bool queued = false;
+    if (__any_sync(0xffffffffu, is_long)) {
+      const int nseg = is_long ? (hb - lb + a.seg - 1) / a.seg : 0;
+      int slot = -1, seg_base = 0;
+      if (is_long && sub == 0) {
+        slot = atomicAdd(a.counters + 0, 1);
+        seg_base = atomicAdd(a.counters + 1, nseg);
+        if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
+          atomicExch(a.counters + 2, 1);
+          slot = -1;
+        } else {
+          a.long_rows[slot] = LongRow{(int)row, seg_base, nseg, a.epoch};
+        }
+      }
+      slot = __shfl_sync(0xffffffffu, slot, grp * LPR);
+      seg_base = __shfl_sync(0xffffffffu, seg_base, grp * LPR);
+      queued = is_long && slot >= 0;
+      if (queued) {
+        for (int s = sub; s < nseg; s += LPR) a.seg_owner[seg_base + s] = slot;
+        hb = lb;
+      } else if (is_long && lb + sub < hb) {  // queue full: done here, the first chunk was not preloaded
+        c = __ldg(a.colind + lb + sub);
+        v = __ldg(a.val + lb + sub);
+      }
+    }
+    V acc[VEC];
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+    accumulate_preloaded<V, LPR, VEC, U, false>(a, lb, hb, sub, grp, 0, nvec, acc, c, v);
+    if (valid && !queued) store_row<V, LPR, VEC>(a, (int)row, sub, 0, nvec, acc);
+    row += G;
+    lb = nlb; hb = nhb; c = cn; v = vn;
+    nlb = nnlb; nhb = nnhb;
+  }
+}
+
+// Second half of the long-row path: one warp per queued row adds that row's partial rows strictly in segment
+// order (the order every path uses, so results do not depend on which kernel ran) and writes the row of C.
+// One vector column per lane, RB partial rows in flight per lane: a hub row with hundreds of segments was the
+// critical path when the last warp to finish a segment did this inside the long-row kernel.
+template <typename V>
+__global__ void __launch_bounds__(256) csrmm_reduce_kernel(const CsrArgs a) {
+  using Ops = VecOps<V>;
+  constexpr int RB = 16;
+  const int lane = threadIdx.x & 31;
+  const int warp = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int nwarps = (int)(((int64_t)gridDim.x * blockDim.x) >> 5);
+  const int nrows = min(*(volatile int*)(a.counters + 0), a.cap_rows);
+  const int nvec_total = (a.K + Ops::W - 1) / Ops::W;
+  const int kpadv = a.Kpad / Ops::W;
+  const V* __restrict__ Pv = reinterpret_cast<const V*>(a.partial);
+  for (int slot = warp; slot < nrows; slot += nwarps) {
+    const LongRow lr = a.long_rows[slot];
+    if (lr.epoch != a.epoch || lr.seg_base < 0 || (int64_t)lr.seg_base + lr.nseg > a.cap_segs) continue;
+    for (int j = lane; j < nvec_total; j += 32) {
+      const V* __restrict__ p = Pv + (int64_t)lr.seg_base * kpadv + j;
+      V acc = Ops::zero();
+      for (int s0 = 0; s0 < lr.nseg; s0 += RB) {
+        V t[RB];
+#pragma unroll
+        for (int jj = 0; jj < RB; ++jj)
+          if (s0 + jj < lr.nseg) t[jj] = __ldcg(p + (int64_t)(s0 + jj) * kpadv);
+#pragma unroll
+        for (int jj = 0; jj < RB; ++jj)
+          if (s0 + jj < lr.nseg) {
+            if (s0 + jj == 0) acc = t[jj]; else Ops::add(acc, t[jj]);
+          }
+      }
+      V* __restrict__ Cv = reinterpret_cast<V*>(a.C) + (int64_t)lr.row * (a.ldc / Ops::W) + j;
+      V out;
+      if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc, a.beta, *Cv);
+      else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc);
+      else out = acc;
+      __stcs(Cv, out);
+    }
+  }
+}
+
 // Long-row kernel: one group per queued segment (all column tiles), partial
-// sums to scratch, last finisher of a row reduces them in segment order.
+// sums to scratch; csrmm_reduce_kernel adds them afterwards.
 template <typename V, int LPR, int VEC, int U>
 __global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
   constexpr int GPW = 32 / LPR;
@@ -235,41 +381,15 @@ __global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
       V acc[VEC];
 #pragma unroll
       for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
-      accumulate_segment<V, LPR, VEC, U>(a, lb, hb, sub, grp, vbase, nvec, acc);
+      accumulate_segment<V, LPR, VEC, U, true>(a, lb, hb, sub, grp, vbase, nvec, acc);
       if (valid) {
 #pragma unroll
         for (int i = 0; i < VEC; ++i)
           if (sub + i * LPR < nvec) Pv[item * kpadv + vbase + sub + i * LPR] = acc[i];
       }
     }
-    // publish, then let the last finisher of the row reduce in segment order
-    __threadfence();
-    __syncwarp();
-    int last = 0;
-    if (valid && sub == 0) last = (atomicAdd(a.done + slot, 1) == lr.nseg - 1);
-    last = __shfl_sync(0xffffffffu, last, grp * LPR);
-    if (last) {
-      __threadfence();
-      if (sub == 0) a.done[slot] = 0;
-      for (int vbase = 0; vbase < nvec_total; vbase += LPR * VEC) {
-        const int nvec = min(LPR * VEC, nvec_total - vbase);
-        V acc[VEC];
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
-        for (int s = 0; s < lr.nseg; ++s) {
-          const V* __restrict__ p = Pv + (int64_t)(lr.seg_base + s) * kpadv + vbase + sub;
-#pragma unroll
-          for (int i = 0; i < VEC; ++i)
-            if (sub + i * LPR < nvec) {
-              if (s == 0) acc[i] = __ldcg(p + i * LPR); else Ops::add(acc[i], __ldcg(p + i * LPR));
-            }
-        }
-        store_row<V, LPR, VEC>(a, lr.row, sub, vbase, nvec, acc);
-      }
-    }
   }
 }
-
 
 // ---------------------------------------------------------------------------
 // Segment queue of the stream path.  Producers (any lane that meets a row longer than `seg`) take a
@@ -694,6 +814,16 @@ __global__ void __launch_bounds__(256, MINB) csrmm_async_kernel(const CsrArgs a)
   }
 }
 
+template <typename V, int LPR, int VEC, int U>
+int launch_long(const CsrArgs& a, int long_ctas, cudaStream_t st) {
+  csrmm_long_kernel<V, LPR, VEC, U><<<long_ctas, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  csrmm_reduce_kernel<V><<<nsm * 2, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
 template <int VEC, int U, int D, int MINB>
 int launch_async(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
   const size_t smem = (size_t)8 * D * U * VEC * 32 * sizeof(float4);
@@ -701,17 +831,15 @@ int launch_async(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
                                       (int)smem));
   csrmm_async_kernel<VEC, U, D, MINB><<<nsm * MINB, 256, smem, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  csrmm_long_kernel<float4, 32, VEC, 8><<<long_ctas, 256, 0, st>>>(a);
-  SPMMDB_CUDA_OK(cudaGetLastError());
-  return SPMMDB_OK;
+  return launch_long<float4, 32, VEC, 8>(a, long_ctas, st);
 }
 
 template <int VEC, int U, int MINB>
 int launch_stream(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
   csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  if (a.inline_segs) csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
-  else csrmm_long_kernel<float4, 32, VEC, (VEC >= 3 ? 4 : 8)><<<long_ctas, 256, 0, st>>>(a);
+  if (!a.inline_segs) return launch_long<float4, 32, VEC, (VEC >= 3 ? 4 : 8)>(a, long_ctas, st);
+  csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
 }
@@ -723,9 +851,16 @@ int launch_variant(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   dim3 grid((unsigned)((a.m + rows_per_cta - 1) / rows_per_cta));
   csrmm_rows_kernel<V, LPR, VEC, U><<<grid, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  csrmm_long_kernel<V, LPR, VEC, U><<<long_ctas, 256, 0, st>>>(a);
+  return launch_long<V, LPR, VEC, U>(a, long_ctas, st);
+}
+
+template <typename V, int LPR, int VEC, int U, int LLPR, int LVEC, int LU>
+int launch_pipe(const CsrArgs& a, int long_ctas, cudaStream_t st) {
+  static const int per_sm = [] { const char* e = getenv("SPMMDB_CSR_PIPE_CTAS"); return e ? atoi(e) : 3; }();
+  const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  csrmm_rows_pipe_kernel<V, LPR, VEC, U><<<nsm * per_sm, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  return SPMMDB_OK;
+  return launch_long<V, LLPR, LVEC, LU>(a, long_ctas, st);
 }
 
 template <typename V>
@@ -737,7 +872,13 @@ int dispatch(const CsrArgs& a, int long_ctas, bool two_rows, cudaStream_t st) {
   // two rows per warp (16 lanes x 2 vectors): a quarter fewer instructions per non-zero than one row per warp, used
   // for small short-row matrices where the call is latency / issue bound (C2: 0.154 -> 0.141 ms against the
   // stream kernel, 0.190 for one row per warp; four rows per warp lose to imbalance inside the warp)
-  if (nvec <= 32 && two_rows) return launch_variant<V, 16, 2, 4>(a, long_ctas, st);
+  if (nvec <= 32 && two_rows) {
+    static const int pipe = [] { const char* e = getenv("SPMMDB_CSR_PIPE"); return e ? atoi(e) : 1; }();
+    if (pipe == 1) return launch_pipe<V, 16, 2, 4, 16, 2, 4>(a, long_ctas, st);
+    if (pipe == 2) return launch_pipe<V, 16, 2, 4, 32, 1, 8>(a, long_ctas, st);
+    if (pipe == 3) return launch_pipe<V, 16, 2, 4, 32, 1, 16>(a, long_ctas, st);
+    return launch_variant<V, 16, 2, 4>(a, long_ctas, st);
+  }
   if (nvec <= 32) return launch_variant<V, 32, 1, 8>(a, long_ctas, st);
   if (nvec <= 64) return launch_variant<V, 32, 2, 8>(a, long_ctas, st);
   if (nvec <= 96) return launch_variant<V, 32, 3, 4>(a, long_ctas, st);
