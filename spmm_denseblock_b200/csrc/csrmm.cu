@@ -48,6 +48,7 @@ struct CsrArgs {
   int epoch;            // call counter: tells this call's queue entries from stale ones
   int rpi;              // stream kernel: rows per work item (<= 32)
   int inline_segs;      // stream kernel: warps take queued segments between items (else: long-row kernel after)
+  int prequeued;        // the long-row queue was built by csrmm_scan_long_kernel: row kernels only skip long rows
 };
 
 template <typename V> struct VecOps;
@@ -262,7 +263,10 @@ __global__ void __launch_bounds__(256, 3) csrmm_rows_pipe_kernel(const CsrArgs a
     const bool valid = row < a.m;
     const bool is_long = (hb - lb) > a.seg;
     bool queued = false;
-    if (__any_sync(0xffffffffu, is_long)) {
+    if (a.prequeued) {
+      queued = is_long;
+      if (queued) hb = lb;
+    } else if (__any_sync(0xffffffffu, is_long)) {
       const int nseg = is_long ? (hb - lb + a.seg - 1) / a.seg : 0;
       int slot = -1, seg_base = 0;
       if (is_long && sub == 0) {
@@ -294,6 +298,56 @@ __global__ void __launch_bounds__(256, 3) csrmm_rows_pipe_kernel(const CsrArgs a
     row += G;
     lb = nlb; hb = nhb; c = cn; v = vn;
     nlb = nnlb; nhb = nnhb;
+  }
+}
+
+// Queue a row longer than `seg` for the long-row kernel (one lane; what csrmm_rows_kernel does with a group).
+// Returns false when the queue is full: the caller then processes the row itself.
+__device__ __forceinline__ bool queue_long_row(const CsrArgs& a, int row, int len) {
+  const int nseg = (len + a.seg - 1) / a.seg;
+  const int slot = atomicAdd(a.counters + 0, 1);
+  const int seg_base = atomicAdd(a.counters + 1, nseg);
+  if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
+    atomicExch(a.counters + 2, 1);
+    return false;
+  }
+  a.long_rows[slot] = LongRow{row, seg_base, nseg, a.epoch};
+  for (int s = 0; s < nseg; ++s) a.seg_owner[seg_base + s] = slot;
+  return true;
+}
+
+// Builds the long-row queue ahead of the row kernels (overlapped small-matrix path): a lane per row, rows longer
+// than `seg` are queued.  With the queue complete before anything else starts, the long-row kernels can run on
+// a second stream next to the rows kernel instead of after it.  A row that does not fit the queue (the caller's
+// nnz was too small) is computed here by the whole warp, one float4 / float column per lane, as the sequential
+// chain over the whole row -- what the rows kernels do with such a row.
+template <typename V>
+__global__ void __launch_bounds__(256) csrmm_scan_long_kernel(const CsrArgs a) {
+  using Ops = VecOps<V>;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+  const int nvec = (a.K + Ops::W - 1) / Ops::W;
+  const V* __restrict__ Bv = reinterpret_cast<const V*>(a.B);
+  const int64_t ldbv = a.ldb / Ops::W;
+  const int64_t rows_padded = ((int64_t)a.m + 31) & ~(int64_t)31;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < rows_padded; row += nthreads) {
+    int lb = 0, hb = 0;
+    if (row < a.m) { lb = __ldg(a.rowptr + row); hb = __ldg(a.rowptr + row + 1); }
+    bool failed = false;
+    if (hb - lb > a.seg) failed = !queue_long_row(a, (int)row, hb - lb);
+    unsigned todo = __ballot_sync(FULL, failed);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const int r = (int)(row - lane + src);
+      const int l0 = __shfl_sync(FULL, lb, src), h0 = __shfl_sync(FULL, hb, src);
+      for (int j = lane; j < nvec; j += 32) {
+        V acc[1] = {Ops::zero()};
+        for (int q = l0; q < h0; ++q) Ops::fma(acc[0], __ldg(a.val + q), __ldg(Bv + (int64_t)__ldg(a.colind + q) * ldbv + j));
+        store_row<V, 32, 1>(a, r, 0, j, nvec - j, acc);
+      }
+    }
   }
 }
 
@@ -854,10 +908,43 @@ int launch_variant(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   return launch_long<V, LPR, VEC, U>(a, long_ctas, st);
 }
 
+// Second stream + fork / join events of the overlapped small-matrix path (created once per process).
+struct Overlap {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool ok = false;
+  Overlap() {
+    ok = cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking) == cudaSuccess &&
+         cudaEventCreateWithFlags(&fork, cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&join, cudaEventDisableTiming) == cudaSuccess;
+  }
+};
+
 template <typename V, int LPR, int VEC, int U, int LLPR, int LVEC, int LU>
 int launch_pipe(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   static const int per_sm = [] { const char* e = getenv("SPMMDB_CSR_PIPE_CTAS"); return e ? atoi(e) : 3; }();
+  static const int overlap_env = [] { const char* e = getenv("SPMMDB_CSR_OVERLAP"); return e ? atoi(e) : 1; }();
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+  if (overlap_env) {
+    // queue first, then the rows kernel on the caller's stream next to the long-row kernels on a side stream:
+    // neither fills the GPU alone (both are latency bound at ~30 % occupancy, profiles/r1o)
+    static Overlap ov;
+    if (ov.ok) {
+      CsrArgs b = a;
+      b.prequeued = 1;
+      csrmm_scan_long_kernel<V><<<nsm * 2, 256, 0, st>>>(b);
+      SPMMDB_CUDA_OK(cudaGetLastError());
+      SPMMDB_CUDA_OK(cudaEventRecord(ov.fork, st));
+      SPMMDB_CUDA_OK(cudaStreamWaitEvent(ov.side, ov.fork, 0));
+      const int rc = launch_long<V, LLPR, LVEC, LU>(b, long_ctas, ov.side);
+      if (rc != SPMMDB_OK) return rc;
+      csrmm_rows_pipe_kernel<V, LPR, VEC, U><<<nsm * per_sm, 256, 0, st>>>(b);
+      SPMMDB_CUDA_OK(cudaGetLastError());
+      SPMMDB_CUDA_OK(cudaEventRecord(ov.join, ov.side));
+      SPMMDB_CUDA_OK(cudaStreamWaitEvent(st, ov.join, 0));
+      return SPMMDB_OK;
+    }
+  }
   csrmm_rows_pipe_kernel<V, LPR, VEC, U><<<nsm * per_sm, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
   return launch_long<V, LLPR, LVEC, LU>(a, long_ctas, st);
@@ -868,18 +955,20 @@ int dispatch(const CsrArgs& a, int long_ctas, bool two_rows, cudaStream_t st) {
   const int nvec = (a.K + VecOps<V>::W - 1) / VecOps<V>::W;
   if (nvec <= 4) return launch_variant<V, 4, 1, 4>(a, long_ctas, st);
   if (nvec <= 8) return launch_variant<V, 8, 1, 8>(a, long_ctas, st);
+  // Small short-row matrices (`two_rows`: under 4 M non-zeros, 32 < K <= 128) are latency / issue bound, not
+  // bandwidth bound (profiles/r1o): two rows per warp (16 lanes each), the pipelined rows kernel, and the
+  // long-row kernels on a side stream.  C2: 0.154 (stream kernel) -> 0.141 (two rows per warp) -> 0.108 ms;
+  // one row per warp 0.190, four rows per warp lose to imbalance inside the warp.
+  static const int pipe = [] { const char* e = getenv("SPMMDB_CSR_PIPE"); return e ? atoi(e) : 1; }();
+  if (nvec <= 16 && two_rows && pipe) return launch_pipe<V, 16, 1, 8, 16, 1, 8>(a, long_ctas, st);
   if (nvec <= 16) return launch_variant<V, 16, 1, 8>(a, long_ctas, st);
-  // two rows per warp (16 lanes x 2 vectors): a quarter fewer instructions per non-zero than one row per warp, used
-  // for small short-row matrices where the call is latency / issue bound (C2: 0.154 -> 0.141 ms against the
-  // stream kernel, 0.190 for one row per warp; four rows per warp lose to imbalance inside the warp)
   if (nvec <= 32 && two_rows) {
-    static const int pipe = [] { const char* e = getenv("SPMMDB_CSR_PIPE"); return e ? atoi(e) : 1; }();
     if (pipe == 1) return launch_pipe<V, 16, 2, 4, 16, 2, 4>(a, long_ctas, st);
     if (pipe == 2) return launch_pipe<V, 16, 2, 4, 32, 1, 8>(a, long_ctas, st);
-    if (pipe == 3) return launch_pipe<V, 16, 2, 4, 32, 1, 16>(a, long_ctas, st);
     return launch_variant<V, 16, 2, 4>(a, long_ctas, st);
   }
   if (nvec <= 32) return launch_variant<V, 32, 1, 8>(a, long_ctas, st);
+  if (nvec <= 64 && two_rows && pipe) return launch_pipe<V, 32, 2, 4, 32, 2, 4>(a, long_ctas, st);
   if (nvec <= 64) return launch_variant<V, 32, 2, 8>(a, long_ctas, st);
   if (nvec <= 96) return launch_variant<V, 32, 3, 4>(a, long_ctas, st);
   return launch_variant<V, 32, 4, 4>(a, long_ctas, st);
@@ -898,6 +987,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
   // ~10 dependent L2 round trips, the grid-stride long-row kernel half of that (0.155 vs 0.194 ms on C2).
   a.inline_segs = a.seg >= 256;
+  a.prequeued = 0;
   a.Kpad = (K + 3) & ~3;
   static int g_epoch = 0;
   a.epoch = ++g_epoch;
@@ -935,7 +1025,8 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   // ceiling there (0.94 ms vs 1.67 ms for the stream kernel, same profile file).
   const bool dense_rows = m > 0 && nnz / m >= 64;
   // small matrices with a 128-wide dense side: the two-rows-per-warp rows kernel (see dispatch)
-  const bool small_k128 = vec4 && nnz < ((int64_t)4 << 20) && K > 64 && K <= 128 && !dense_rows;
+  static const int small_env = [] { const char* e = getenv("SPMMDB_CSR_SMALL"); return e ? atoi(e) : 1; }();
+  const bool small_k128 = small_env && vec4 && nnz < ((int64_t)4 << 20) && K > 32 && K <= 256 && !dense_rows;
   if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows && !small_k128) {
     // rows per item: measured on B200 (profiles/r1b_csr_rpi_sweep.txt): 8 rows is the best or within 3% of it
     // for avg degree 2 (C4), 6.5 (C2) and 24 (C5); fewer rows per item for denser rows.

@@ -394,6 +394,26 @@ def test_csrmm_scratch_reuse_across_sizes(pkg, oracle, K):
             assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32, (order, i)
 
 
+@pytest.mark.parametrize("K", [64, 128, 256, 300])
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.5, 2.0)])
+def test_csrmm_understated_nnz_overflows_the_long_row_queue(pkg, oracle, K, alpha, beta):
+    """The long-row queue is sized from the caller's nnz.  A caller that understates it (here: 64 for a matrix
+    with four hub rows) overflows the queue; rows that do not fit are computed in place by the kernel that
+    found them -- on the overlapped small-matrix path that is the queue-building pre-pass."""
+    rng = np.random.default_rng(K)
+    m = 2500
+    rp, ci, v = random_csr(rng, m, m, 6, hubs={1: 2000, 700: 900, 701: 300, 2499: 130})
+    B = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    ref = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=alpha, beta=beta)
+    scale = abs(alpha) * oracle.csrmm(rp, ci, np.abs(v), np.abs(B), K) + abs(beta) * np.abs(C0)
+    for nnz in (64, 200, None):
+        C = dev(C0.copy())
+        pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, m, K, alpha=alpha, beta=beta, nnz=nnz)
+        err = np.max(np.abs(C.cpu().numpy().astype(np.float64) - ref) / np.maximum(scale, 1e-30))
+        assert err <= TOL_FP32, (nnz, err)
+
+
 @pytest.mark.parametrize("K,alpha,beta", [(256, 1.0, 0.0), (256, 0.5, 2.0), (128, 1.0, 0.0), (100, 1.0, 0.0)])
 def test_csrmm_host_entry_slab_pipeline(pkg, oracle, K, alpha, beta):
     """spmmdb_csrmm_host_f32 (host buffers; feature slabs copied / computed / copied back in a pipeline when

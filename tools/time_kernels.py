@@ -21,7 +21,13 @@ def timeit(fn, warmup=3, iters=10, flush=None):
     ts = []
     for _ in range(iters):
         if flush is not None:
-            flush.add_(1.0)
+            mode = os.environ.get("SPMMDB_FLUSH", "write")
+            if mode == "write":        # L2 left full of DIRTY lines (their write-back lands inside the timed call)
+                flush.add_(1.0)
+            elif mode == "read":       # L2 left full of clean lines of another buffer
+                flush.add_(1.0)
+                flush.sum()
+            # "warm": nothing -- the previous call's B / C stay in L2
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s.record()
         fn()
