@@ -75,6 +75,29 @@ def test_run_csrmm_cli_and_agreement(graph_dir):
 
 
 @pytest.mark.gpu
+def test_run_csrmm_reads_the_binary_cache(graph_dir, tmp_path):
+    """drivers/graph2bin writes tmp/<graph>.csrbin; the drivers then load it instead of parsing the text pair
+    (SPMMDB_GRAPH_AUTO) and print the same result."""
+    import shutil
+    _build()
+    cwd, n, nnz = graph_dir
+    work = tmp_path / "w"
+    shutil.copytree(os.path.join(cwd, "tmp"), work / "tmp")
+    rc, out_text = _run([os.path.join(BIN, "run_csrmm"), "toy", "128", "gespmm", "1"], str(work))
+    assert rc == 0, out_text
+    rc, out = _run([os.path.join(BIN, "graph2bin"), "tmp/toy"], str(work))
+    assert rc == 0 and f"n = {n} nnz = {nnz}" in out, out
+    os.remove(work / "tmp" / "toy_indices.txt")  # only the binary file can serve the graph now
+    rc, out_bin = _run([os.path.join(BIN, "run_csrmm"), "toy", "128", "gespmm", "1"], str(work))
+    assert rc == 0, out_bin
+    assert f"n={n} nnz={nnz}" in out_bin
+    assert _checksum(out_bin) == _checksum(out_text)
+    os.remove(work / "tmp" / "toy.csrbin")
+    rc, out = _run([os.path.join(BIN, "run_csrmm"), "toy", "128", "gespmm", "1"], str(work))
+    assert rc != 0  # missing graph files fail loudly instead of running on garbage
+
+
+@pytest.mark.gpu
 def test_run_bsrmm_cli_and_agreement(graph_dir):
     _build()
     cwd, n, nnz = graph_dir
