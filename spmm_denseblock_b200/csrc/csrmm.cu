@@ -17,6 +17,8 @@
 // result is deterministic and independent of any row sharding.
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace spmmdb {
@@ -928,8 +930,19 @@ int launch_pipe(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   if (overlap_env) {
     // queue first, then the rows kernel on the caller's stream next to the long-row kernels on a side stream:
     // neither fills the GPU alone (both are latency bound at ~30 % occupancy, profiles/r1o)
-    static Overlap ov;
-    if (ov.ok) {
+    // one side stream per device: created lazily on the device that is current for this call
+    static Overlap* per_dev[64] = {};
+    static std::mutex mu;
+    int devid = 0;
+    if (cudaGetDevice(&devid) != cudaSuccess || devid < 0 || devid >= 64) devid = -1;
+    Overlap* ovp = nullptr;
+    if (devid >= 0) {
+      std::lock_guard<std::mutex> lk(mu);
+      if (per_dev[devid] == nullptr) per_dev[devid] = new Overlap();
+      ovp = per_dev[devid];
+    }
+    if (ovp != nullptr && ovp->ok) {
+      Overlap& ov = *ovp;
       CsrArgs b = a;
       b.prequeued = 1;
       csrmm_scan_long_kernel<V><<<nsm * 2, 256, 0, st>>>(b);
