@@ -5,7 +5,7 @@
 //
 // The bs rows of a block row are one contiguous piece of the CSR arrays, so the CTA reads them
 // coalesced instead of one lane walking one row.  The set of column blocks the block row touches
-// is a bitmap in shared memory (atomicOr per entry); a prefix sum of the per-word popcounts turns
+// is a bitmap in shared memory (atomicOr per entry whose bit is not set yet); a prefix sum of the per-word popcounts turns
 // the bitmap into ranks: the t-th set bit is the t-th non-zero block, ascending, with no sort and
 // no merge.  Values are scattered into the block row's piece of bsr_val right after the same CTA
 // zero-filled it (the lines are still in L2, DRAM sees each line once).  The split additionally
@@ -110,7 +110,10 @@ __global__ void __launch_bounds__(kThreads) csr2bsr_br_kernel(const BrArgs a) {
     int lo = INT_MAX, hi = -1;
     for (int idx = s0 + threadIdx.x; idx < s1; idx += kThreads) {
       const int blk = blk_of(__ldg(a.colind + idx), bs, a.shift, a.last);
-      atomicOr(bm + (blk >> 5), 1u << (blk & 31));
+      // most entries of a dense block row find their block's bit already set: look before the atomic, or every
+      // thread of the CTA serialises on the same one or two bitmap words
+      const unsigned bit = 1u << (blk & 31);
+      if (!(*(volatile unsigned*)(bm + (blk >> 5)) & bit)) atomicOr(bm + (blk >> 5), bit);
       lo = min(lo, blk >> 5); hi = max(hi, blk >> 5);
     }
 #pragma unroll
@@ -178,7 +181,10 @@ __global__ void __launch_bounds__(kThreads) divide_br_kernel(const BrArgs a) {
     int lo = INT_MAX, hi = -1;
     for (int idx = s0 + threadIdx.x; idx < s1; idx += kThreads) {
       const int blk = blk_of(__ldg(a.colind + idx), bs, a.shift, a.last);
-      atomicOr(bm + (blk >> 5), 1u << (blk & 31));
+      // most entries of a dense block row find their block's bit already set: look before the atomic, or every
+      // thread of the CTA serialises on the same one or two bitmap words
+      const unsigned bit = 1u << (blk & 31);
+      if (!(*(volatile unsigned*)(bm + (blk >> 5)) & bit)) atomicOr(bm + (blk >> 5), bit);
       lo = min(lo, blk >> 5); hi = max(hi, blk >> 5);
     }
 #pragma unroll
