@@ -92,6 +92,7 @@ __device__ __forceinline__ void accumulate_preloaded(const Args& a, int lb, int 
 #pragma unroll
   for (int i = 0; i < VEC; ++i) colok[i] = (sub + i * LPR) < nvec;
 
+  static_assert(LPR % U == 0, "a gather batch must not straddle two chunks");
   for (int base = lb; __any_sync(0xffffffffu, base < hb); base += LPR) {
     const int nidx = base + LPR + sub;
     int cn = 0;
