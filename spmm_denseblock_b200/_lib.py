@@ -45,6 +45,8 @@ SIGNATURES = {
     "spmmdb_graph_read": [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(c_i64), C.POINTER(vp), C.POINTER(vp)],
     "spmmdb_graph_write": [C.c_char_p, C.c_int, C.c_int, c_i64, vp, vp],
     "spmmdb_graph_free": [vp],
+    "spmmdb_set_tuning": [C.c_char_p, C.c_int],
+    "spmmdb_get_tuning": [C.c_char_p, C.c_int],
     "spmmdb_version": [],
     "spmmdb_last_error": [],
     "spmmdb_device_sm": [],

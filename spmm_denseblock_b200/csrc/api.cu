@@ -24,7 +24,9 @@ __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict_
                                                         int64_t ldo, int rows, int cols, float beta) {
   __shared__ float tile[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-  const int64_t r0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+  // 1-D grid over the tiles (either dimension may exceed the 65535 limit of grid.y: C5 has 76 533 row tiles)
+  const int64_t tiles_r = ((int64_t)rows + 31) / 32;
+  const int64_t r0 = ((int64_t)blockIdx.x % tiles_r) * 32, c0 = ((int64_t)blockIdx.x / tiles_r) * 32;
   for (int i = ty; i < 32; i += 8) {
     const int64_t c = c0 + i, r = r0 + tx;
     tile[i][tx] = (c < cols && r < rows) ? in[c * ldi + r] : 0.f;
@@ -44,28 +46,22 @@ __global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict_
 int transpose(const float* in, int64_t ldi, float* out, int64_t ldo, int rows, int cols, float beta,
               cudaStream_t st) {
   if (rows == 0 || cols == 0) return SPMMDB_OK;
-  dim3 grid((unsigned)((rows + 31) / 32), (unsigned)((cols + 31) / 32));
-  transpose_kernel<<<grid, 256, 0, st>>>(in, ldi, out, ldo, rows, cols, beta);
+  const int64_t tiles = (((int64_t)rows + 31) / 32) * (((int64_t)cols + 31) / 32);
+  if (tiles > 0x7fffffffLL) return SPMMDB_ERR_INVALID_VALUE;
+  transpose_kernel<<<(unsigned)tiles, 256, 0, st>>>(in, ldi, out, ldo, rows, cols, beta);
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
 }
 
-struct NnzCache { const int* rowptr; int m; int64_t nnz; int dev; };
-NnzCache g_nnz_cache[8];
-int g_nnz_cache_next = 0;
-
-// nnz = rowptr[m] when the caller does not know it (gespmm_csrmm's signature has
-// no nnz).  One 4-byte read-back per distinct (rowptr, m); later calls are async.
+// nnz = rowptr[m] when the caller does not know it (gespmm_csrmm's signature has no nnz): one 4-byte
+// read-back per call, which synchronises `st`.  (A cache keyed by the rowptr address served a stale nnz when
+// an allocator handed the same address to another graph, and nnz decides the row segmentation.)  Callers
+// that know nnz pass it and stay asynchronous.
 int resolve_nnz(const int* rowptr, int m, cudaStream_t st, int64_t* nnz) {
-  int dev = 0;
-  cudaGetDevice(&dev);
-  for (auto& e : g_nnz_cache)
-    if (e.rowptr == rowptr && e.m == m && e.dev == dev && e.rowptr != nullptr) { *nnz = e.nnz; return SPMMDB_OK; }
   int h = 0;
   SPMMDB_CUDA_OK(cudaMemcpyAsync(&h, rowptr + m, sizeof(int), cudaMemcpyDeviceToHost, st));
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
-  g_nnz_cache[g_nnz_cache_next] = NnzCache{rowptr, m, h, dev};
-  g_nnz_cache_next = (g_nnz_cache_next + 1) % 8;
+  if (h < 0) return SPMMDB_ERR_INVALID_VALUE;
   *nnz = h;
   return SPMMDB_OK;
 }

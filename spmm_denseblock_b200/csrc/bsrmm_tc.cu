@@ -730,10 +730,10 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
 
   TcArgs a;
   a.mb = mb; a.n = n; a.bs = bs; a.tiles = tiles; a.nchunks = nchunks;
-  static const int nt_env = [] { const char* e = getenv("SPMMDB_BSR_NT"); return e ? atoi(e) : 0; }();
+  const int nt_env = SPMMDB_TUNE("BSR_NT", 0);
   // Two CTAs per SM (256 TMEM columns and half the shared memory each) hide the per-step latency of
   // the single MMA-issuing warp; they need tiles * NT <= 128 per accumulator buffer.
-  static const int cps_env = [] { const char* e = getenv("SPMMDB_BSR_CTAS_PER_SM"); return e ? atoi(e) : 0; }();
+  const int cps_env = SPMMDB_TUNE("BSR_CTAS_PER_SM", 0);
   int cps = (cps_env == 1 || cps_env == 2) ? cps_env : (tiles == 1 ? 2 : 1);
   if (tiles > 2 || (128 / tiles) < bs) cps = 1;
   const int acc_max = cps == 2 ? 128 : 256;  // accumulator columns per buffer (two buffers)
@@ -744,7 +744,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   a.tmem_cols = cps == 2 ? 256 : 512;
   a.NT = NT;
   a.G = NT / bs;
-  static const int dbg_env = [] { const char* e = getenv("SPMMDB_BSR_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+  const int dbg_env = SPMMDB_TUNE("BSR_DEBUG_SKIP", 0);
   a.dbg = dbg_env;
   a.dir = dir; a.c_layout = c_layout;
   a.num_super = (mb + a.G - 1) / a.G;
@@ -781,7 +781,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
 
   CUtensorMap mapB, mapA;
   a.b_one = (n % fc == 0) ? 1 : 0;
-  static const int b3d_env = [] { const char* e = getenv("SPMMDB_BSR_B3D"); return e ? atoi(e) : 1; }();
+  const int b3d_env = SPMMDB_TUNE("BSR_B3D", 1);
   if (!b3d_env) a.b_one = 0;
   if (a.b_one && !make_map_b3d(&mapB, bf16, Bt, (uint64_t)fc, (uint64_t)krows, (uint64_t)nchunks,
                                (uint64_t)ldbt * esize, (uint32_t)bs))
@@ -795,7 +795,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
 
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   const int grid = a.num_super < nsm * cps ? a.num_super : nsm * cps;
-  static const int p_env = [] { const char* e = getenv("SPMMDB_BSR_PRODUCERS"); return e ? atoi(e) : 0; }();
+  const int p_env = SPMMDB_TUNE("BSR_PRODUCERS", 0);
   const int P = p_env >= 1 && p_env <= 3 ? p_env : 3;  // 4 producers with 3 stages did not finish in the r1l sweep: not offered
   if (bf16) {
     if (P == 1) return launch_tc<true, 1>(a, mapB, mapA, grid, smem_bytes, st);

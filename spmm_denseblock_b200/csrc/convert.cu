@@ -15,6 +15,8 @@
 #include <limits.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace spmmdb {
@@ -521,9 +523,11 @@ int divide_br(bool fill, int dir, int m, int n, const int* rowptr, const int* co
 struct ConvNote { const int* rowptr; int m, bs, dev; int64_t nnz, nnzb; };
 static ConvNote g_conv_notes[8];
 static int g_conv_next = 0;
+static std::mutex g_conv_mu;  // the notes are a hint between two equivalent kernels: a stale one costs time only
 static void conv_note(const int* rowptr, int m, int bs, int64_t nnz, int64_t nnzb) {
   int dev = 0;
   cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lk(g_conv_mu);
   for (auto& e : g_conv_notes)
     if (e.rowptr == rowptr && e.m == m && e.bs == bs && e.dev == dev) { e.nnz = nnz; e.nnzb = nnzb; return; }
   g_conv_notes[g_conv_next] = ConvNote{rowptr, m, bs, dev, nnz, nnzb};
@@ -532,6 +536,7 @@ static void conv_note(const int* rowptr, int m, int bs, int64_t nnz, int64_t nnz
 static bool conv_lookup(const int* rowptr, int m, int bs, int64_t* nnz, int64_t* nnzb) {
   int dev = 0;
   cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lk(g_conv_mu);
   for (auto& e : g_conv_notes)
     if (e.rowptr == rowptr && e.rowptr != nullptr && e.m == m && e.bs == bs && e.dev == dev) {
       *nnz = e.nnz; *nnzb = e.nnzb;
@@ -637,7 +642,7 @@ extern "C" int spmmdb_bsr2csr_f32(int dir, int mb, int nb, const int* bsr_rowptr
   cudaStream_t st = (cudaStream_t)stream;
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   const bool aligned = ((((uintptr_t)bsr_val) | ((uintptr_t)csr_val) | ((uintptr_t)csr_colind)) & 15) == 0;
-  static const int force_scalar = getenv("SPMMDB_BSR2CSR_SCALAR") ? atoi(getenv("SPMMDB_BSR2CSR_SCALAR")) : 0;
+  const int force_scalar = SPMMDB_TUNE("BSR2CSR_SCALAR", 0);
   if (dir == SPMMDB_DIR_ROW && aligned && !force_scalar &&
       (block_dim == 8 || block_dim == 16 || block_dim == 32 || block_dim == 64)) {
     // a warp's run of blocks: ~16 KB of block values, so the one binary search per run is noise

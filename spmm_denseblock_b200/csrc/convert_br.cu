@@ -295,7 +295,7 @@ int launch_br(K kernel, const BrArgs& a, size_t smem, cudaStream_t st) {
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   int per_sm = (int)((200 * 1024) / (smem + 1024));
   per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
-  static const int cap_env = [] { const char* e = getenv("SPMMDB_CONVERT_BR_CTAS"); return e ? atoi(e) : 0; }();
+  const int cap_env = SPMMDB_TUNE("CONVERT_BR_CTAS", 0);
   if (cap_env > 0 && per_sm > cap_env) per_sm = cap_env;
   const int grid = a.mb < nsm * per_sm ? a.mb : nsm * per_sm;
   kernel<<<grid, kThreads, smem, st>>>(a);

@@ -17,7 +17,10 @@
 // result is deterministic and independent of any row sharding.
 #include <stdlib.h>
 
+#include <atomic>
+#include <map>
 #include <mutex>
+#include <utility>
 
 #include "common.cuh"
 
@@ -925,22 +928,24 @@ struct Overlap {
 
 template <typename V, int LPR, int VEC, int U, int LLPR, int LVEC, int LU>
 int launch_pipe(const CsrArgs& a, int long_ctas, cudaStream_t st) {
-  static const int per_sm = [] { const char* e = getenv("SPMMDB_CSR_PIPE_CTAS"); return e ? atoi(e) : 3; }();
-  static const int overlap_env = [] { const char* e = getenv("SPMMDB_CSR_OVERLAP"); return e ? atoi(e) : 1; }();
+  const int per_sm = SPMMDB_TUNE("CSR_PIPE_CTAS", 3);
+  const int overlap_env = SPMMDB_TUNE("CSR_OVERLAP", 1);
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   if (overlap_env) {
     // queue first, then the rows kernel on the caller's stream next to the long-row kernels on a side stream:
     // neither fills the GPU alone (both are latency bound at ~30 % occupancy, profiles/r1o)
-    // one side stream per device: created lazily on the device that is current for this call
-    static Overlap* per_dev[64] = {};
+    // one side stream + event pair per (device, caller stream), created lazily: two caller streams in flight
+    // together must not share the fork / join events
+    static std::map<std::pair<int, cudaStream_t>, Overlap*> per_stream;
     static std::mutex mu;
     int devid = 0;
-    if (cudaGetDevice(&devid) != cudaSuccess || devid < 0 || devid >= 64) devid = -1;
+    if (cudaGetDevice(&devid) != cudaSuccess) devid = -1;
     Overlap* ovp = nullptr;
     if (devid >= 0) {
       std::lock_guard<std::mutex> lk(mu);
-      if (per_dev[devid] == nullptr) per_dev[devid] = new Overlap();
-      ovp = per_dev[devid];
+      Overlap*& slot = per_stream[std::make_pair(devid, st)];
+      if (slot == nullptr && per_stream.size() <= 64) slot = new Overlap();
+      ovp = slot;
     }
     if (ovp != nullptr && ovp->ok) {
       Overlap& ov = *ovp;
@@ -973,7 +978,7 @@ int dispatch(const CsrArgs& a, int long_ctas, bool two_rows, cudaStream_t st) {
   // bandwidth bound (profiles/r1o): two rows per warp (16 lanes each), the pipelined rows kernel, and the
   // long-row kernels on a side stream.  C2: 0.154 (stream kernel) -> 0.141 (two rows per warp) -> 0.108 ms;
   // one row per warp 0.190, four rows per warp lose to imbalance inside the warp.
-  static const int pipe = [] { const char* e = getenv("SPMMDB_CSR_PIPE"); return e ? atoi(e) : 1; }();
+  const int pipe = SPMMDB_TUNE("CSR_PIPE", 1);
   if (nvec <= 16 && two_rows && pipe) return launch_pipe<V, 16, 1, 8, 16, 1, 8>(a, long_ctas, st);
   if (nvec <= 16) return launch_variant<V, 16, 1, 8>(a, long_ctas, st);
   if (nvec <= 32 && two_rows) {
@@ -997,14 +1002,15 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   CsrArgs a;
   a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
-  a.seg = spmmdb_get_csrmm_segment() ? spmmdb_get_csrmm_segment() : spmmdb_csrmm_segment_for(m, nnz);
+  const int seg_override = current_segment_override();
+  a.seg = seg_override ? seg_override : spmmdb_csrmm_segment_for(m, nnz);
   // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
   // ~10 dependent L2 round trips, the grid-stride long-row kernel half of that (0.155 vs 0.194 ms on C2).
-  a.inline_segs = a.seg >= 256;
+  const int inline_force = SPMMDB_TUNE("CSR_INLINE", -1);  // -1: automatic
+  a.inline_segs = inline_force >= 0 ? (inline_force != 0) : (a.seg >= 256);
   a.prequeued = 0;
   a.Kpad = (K + 3) & ~3;
-  static int g_epoch = 0;
-  a.epoch = ++g_epoch;
+  a.epoch = next_epoch();
   // worst case: every segment queued.  segments <= nnz/seg + long rows, long rows <= nnz/seg
   const int64_t max_long = nnz / a.seg + 1;
   const int64_t max_segs = 2 * max_long;
@@ -1030,16 +1036,16 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.partial = part;
   SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
-  static const int lc_env = [] { const char* e = getenv("SPMMDB_CSR_LONG_CTAS"); return e ? atoi(e) : 0; }();
+  const int lc_env = SPMMDB_TUNE("CSR_LONG_CTAS", 0);
   const int long_ctas = nsm * (lc_env > 0 ? lc_env : 4);  // C2 sweep: 2 / 4 / 8 -> 0.166 / 0.160 / 0.156 ms
   const bool vec4 = (K % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
                     (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
-  static const int stream_min_k = [] { const char* e = getenv("SPMMDB_CSR_STREAM_MIN_K"); return e ? atoi(e) : 32; }();
+  const int stream_min_k = SPMMDB_TUNE("CSR_STREAM_MIN_K", 32);
   // Long average rows (C3: 271 nnz/row) keep one warp per row: the rows kernel reaches the L2 gather
   // ceiling there (0.94 ms vs 1.67 ms for the stream kernel, same profile file).
   const bool dense_rows = m > 0 && nnz / m >= 64;
   // small matrices with a 128-wide dense side: the two-rows-per-warp rows kernel (see dispatch)
-  static const int small_env = [] { const char* e = getenv("SPMMDB_CSR_SMALL"); return e ? atoi(e) : 1; }();
+  const int small_env = SPMMDB_TUNE("CSR_SMALL", 1);
   const bool small_k128 = small_env && vec4 && nnz < ((int64_t)4 << 20) && K > 32 && K <= 256 && !dense_rows;
   if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows && !small_k128) {
     // rows per item: measured on B200 (profiles/r1b_csr_rpi_sweep.txt): 8 rows is the best or within 3% of it
@@ -1047,11 +1053,11 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;
     int rpi = 8;
     while (rpi > 1 && rpi * avg > 512) rpi >>= 1;
-    static const int rpi_env = [] { const char* e = getenv("SPMMDB_CSR_RPI"); return e ? atoi(e) : 0; }();
+    const int rpi_env = SPMMDB_TUNE("CSR_RPI", 0);
     if (rpi_env > 0) rpi = rpi_env < 32 ? rpi_env : 32;
     a.rpi = rpi;
     const int vec = (K / 4 + 31) / 32;
-    static const int async_env = [] { const char* e = getenv("SPMMDB_CSR_ASYNC"); return e ? atoi(e) : 0; }();
+    const int async_env = SPMMDB_TUNE("CSR_ASYNC", 0);
     if (async_env && vec <= 2) {
       // ring per warp = D*U rows; 2 CTAs/SM x 8 warps x 12 KB = 192 KB in flight
       if (vec == 1) {
@@ -1063,7 +1069,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
       if (async_env == 3) return launch_async<2, 4, 2, 3>(a, nsm, long_ctas, st);
       return launch_async<2, 4, 3, 2>(a, nsm, long_ctas, st);
     }
-    static const int variant = [] { const char* e = getenv("SPMMDB_CSR_VARIANT"); return e ? atoi(e) : 0; }();
+    const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
     if (vec == 1) {
       if (variant == 1) return launch_stream<1, 16, 2>(a, nsm, long_ctas, st);
       if (variant == 3) return launch_stream<1, 8, 4>(a, nsm, long_ctas, st);
@@ -1084,7 +1090,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
 }  // namespace spmmdb
 
 extern "C" int spmmdb_csrmm_segment(int64_t nnz) {
-  static const int seg_env = [] { const char* e = getenv("SPMMDB_CSR_SEG"); return e ? atoi(e) : 0; }();
+  const int seg_env = SPMMDB_TUNE("CSR_SEG", 0);
   if (seg_env >= 32 && (seg_env & (seg_env - 1)) == 0) return seg_env;  // tuning knob (power of two)
   if (nnz < (int64_t)4 << 20) return 64;
   if (nnz < (int64_t)32 << 20) return 256;
@@ -1103,10 +1109,18 @@ extern "C" int spmmdb_csrmm_segment_for(int m, int64_t nnz) {
   return seg;
 }
 
-namespace { int g_segment_override = 0; }
+namespace spmmdb {
+namespace {
+std::atomic<int> g_segment_override{0};
+thread_local int tl_segment_override = 0;  // set by a library entry point around its own inner calls
+}  // namespace
+int current_segment_override() { return tl_segment_override ? tl_segment_override : g_segment_override.load(); }
+ScopedSegment::ScopedSegment(int seg) : before_(tl_segment_override) { tl_segment_override = seg; }
+ScopedSegment::~ScopedSegment() { tl_segment_override = before_; }
+}  // namespace spmmdb
 extern "C" int spmmdb_set_csrmm_segment(int seg) {
   if (seg != 0 && (seg < 32 || (seg & (seg - 1)) != 0)) return SPMMDB_ERR_INVALID_VALUE;
-  g_segment_override = seg;
+  spmmdb::g_segment_override.store(seg);
   return SPMMDB_OK;
 }
-extern "C" int spmmdb_get_csrmm_segment(void) { return g_segment_override; }
+extern "C" int spmmdb_get_csrmm_segment(void) { return spmmdb::g_segment_override.load(); }

@@ -35,7 +35,7 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   // Feature slabs: columns [c0, c0 + Ks) of C need only the same columns of B, so the host<->device copies of one
   // slab overlap the kernel and the opposite-direction copy of its neighbours (PCIe is full duplex): the call costs
   // about H2D(A) + H2D(B) + D2H(one slab) instead of H2D(A) + H2D(B) + kernel + D2H(C).
-  static const int slabs_env = [] { const char* e = getenv("SPMMDB_HOST_SLABS"); return e ? atoi(e) : 0; }();
+  const int slabs_env = SPMMDB_TUNE("HOST_SLABS", 0);
   int slabs = slabs_env > 0 ? slabs_env : 4;
   while (slabs > 1 && (K % slabs != 0 || (K / slabs) % 64 != 0)) slabs >>= 1;  // >= 256-byte rows for the DMA engines
   if (slabs <= 1) {
@@ -67,8 +67,8 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   const int Ks = K / slabs;
   const size_t pitch = sizeof(float) * (size_t)K, width = sizeof(float) * (size_t)Ks;
   // the kernels of all slabs share the whole call's segment length (same bits as the one-shot call)
-  const int seg_before = spmmdb_get_csrmm_segment();
-  if (seg_before == 0) spmmdb_set_csrmm_segment(spmmdb_csrmm_segment_for(m, nnz));
+  const int seg_now = current_segment_override();
+  ScopedSegment pin(seg_now ? seg_now : spmmdb_csrmm_segment_for(m, nnz));
   int rc = SPMMDB_OK;
   for (int sl = 0; sl < slabs && rc == SPMMDB_OK; ++sl) {
     const size_t off = (size_t)sl * Ks;
@@ -87,7 +87,6 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
       e = cudaMemcpy2DAsync(h_C + off, pitch, dC + off, pitch, width, (size_t)m, cudaMemcpyDeviceToHost, s_out);
     if (e != cudaSuccess) { set_last_error("host slab copy", e, __FILE__, __LINE__); rc = SPMMDB_ERR_CUDA; }
   }
-  if (seg_before == 0) spmmdb_set_csrmm_segment(0);
   cudaStreamSynchronize(st);
   cudaStreamSynchronize(s_run);
   cudaError_t e = cudaStreamSynchronize(s_out);

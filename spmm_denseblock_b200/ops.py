@@ -44,6 +44,16 @@ def set_csrmm_segment(seg):
     check(lib().spmmdb_set_csrmm_segment(int(seg)), "spmmdb_set_csrmm_segment")
 
 
+def set_tuning(name, value=None):
+    """Override a tuning knob (None clears it): spmmdb_set_tuning."""
+    v = -2147483648 if value is None else int(value)
+    check(lib().spmmdb_set_tuning(name.encode(), v), "spmmdb_set_tuning")
+
+
+def get_tuning(name, default=0):
+    return lib().spmmdb_get_tuning(name.encode(), int(default))
+
+
 def csrmm(rowptr, colind, val, B, C_out, m, k, K, ldb=None, b_layout=ROW_MAJOR, ldc=None, c_layout=ROW_MAJOR,
           alpha=1.0, beta=0.0, nnz=None):
     """C = alpha*A*B + beta*C with explicit layouts (spmmdb_csrmm_f32)."""

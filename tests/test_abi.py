@@ -49,6 +49,18 @@ def test_version_and_status(L):
     assert L.spmmdb_get_csrmm_segment() == 1024 and L.spmmdb_set_csrmm_segment(0) == 0
 
 
+def test_tuning_knobs(L, monkeypatch):
+    """spmmdb_set_tuning overrides the environment, INT_MIN clears the override."""
+    assert L.spmmdb_get_tuning(b"NO_SUCH_KNOB", 7) == 7
+    monkeypatch.setenv("SPMMDB_NO_SUCH_KNOB", "5")
+    assert L.spmmdb_get_tuning(b"NO_SUCH_KNOB", 7) == 5
+    assert L.spmmdb_set_tuning(b"NO_SUCH_KNOB", 3) == 0 and L.spmmdb_get_tuning(b"NO_SUCH_KNOB", 7) == 3
+    assert L.spmmdb_set_tuning(b"NO_SUCH_KNOB", -2**31) == 0 and L.spmmdb_get_tuning(b"NO_SUCH_KNOB", 7) == 5
+    assert L.spmmdb_set_tuning(None, 1) == -1
+    # the drop-in BSR default arithmetic is the tensor-core path
+    assert L.spmmdb_get_bsrmm_math() in (0, 1, 2)
+
+
 def test_validation_without_device(L):
     z = C.c_void_p(0)
     # negative sizes / bad layout -> INVALID_VALUE before any CUDA call (rocsparse_bsrmm.h:146-148)
@@ -67,7 +79,7 @@ def test_validation_without_device(L):
 def test_product_does_not_touch_oracle():
     """The product tree must not import, link or mention the oracle."""
     bad = []
-    for base in ("spmm_denseblock_b200", "include", "drivers"):
+    for base in ("spmm_denseblock_b200", "include", "drivers", "baseline"):
         for dp, _, fns in os.walk(os.path.join(ROOT, base)):
             if "build" in dp.split(os.sep):
                 continue

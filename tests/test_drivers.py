@@ -141,10 +141,15 @@ def test_microbench_drivers_print_reference_lines(tmp_path):
     for tb in (0, 1):
         sums = []
         for impl in ("rocsparse", "cusparse"):
-            rc, out = _run([os.path.join(BIN, "test_bsrmm"), "0.0005", "16", "64", impl, str(tb)], str(tmp_path))
+            rc, out = _run([os.path.join(BIN, "test_bsrmm"), "0.0005", "16", "64", impl, str(tb)], str(tmp_path),
+                           {"SPMMDB_BSRMM_MATH": "fp32"})
             assert rc == 0 and re.search(r"bsrmm cost time: \d+\.\d{10} ms\nGFLOPs: \d+\.\d{10}", out), out
             sums.append(_checksum(out))
         assert abs(sums[0] - sums[1]) <= 1e-3 * max(1.0, abs(sums[1]))
+        # the drop-in default arithmetic is the tcgen05 tf32 kernel (stated 1e-2)
+        rc, out = _run([os.path.join(BIN, "test_bsrmm"), "0.0005", "16", "64", "rocsparse", str(tb)], str(tmp_path))
+        assert rc == 0, out
+        assert abs(_checksum(out) - sums[1]) <= 2e-2 * max(1.0, abs(sums[1])) + 1.0
     rc, out = _run([os.path.join(BIN, "test_block_cublas"), "0.0005", "16", "64"], str(tmp_path))
     assert rc == 0 and "block gemm cost time" in out, out
 

@@ -1,0 +1,227 @@
+"""Parity of the kernels the benchmark times.
+
+`csrmm_stream_kernel<VEC, U, MINB>` with the inline segment queue (semaphore + tickets + partial sums added
+by the last finisher) is what BENCH / SCALE measure on the products-shaped graph; it is taken only for
+nnz >= 4 M.  These tests force it on small matrices (tuning knobs CSR_SMALL = 0, CSR_INLINE = 1, segment 256)
+for every VEC, and run it at its natural size on config-shaped inputs; every result is compared with the fp64
+oracle (<= 1e-5 relative to sum |a||b|, gespmm_csrmm.h:95-166 semantics), bit for bit with the reference
+kernel's sequential fp32 FMA chain on rows of at most one segment, twice (determinism) and against row shards.
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import random_csr
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-5
+TOL_TC = 1e-2
+TOL_BF16B = 1e-2  # CSR with bf16-stored B (fp32 accumulate): B is rounded to 8 mantissa bits
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import spmm_denseblock_b200 as p
+    assert torch.cuda.is_available()
+    p.lib()
+    return p
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def err_vs(oracle, got, ref64, rp, ci, v, Bm, K, alpha=1.0, beta=0.0, C0=None):
+    scale = abs(alpha) * oracle.csrmm(rp, ci, np.abs(v), np.abs(Bm), K)
+    if C0 is not None:
+        scale = scale + abs(beta) * np.abs(C0)
+    return float(np.max(np.abs(got.astype(np.float64) - ref64) / np.maximum(scale, 1e-30)))
+
+
+@pytest.fixture
+def forced_stream(pkg):
+    """Small matrices through the benchmark's kernel: no small-matrix path, segments of 256 taken inline."""
+    pkg.set_tuning("CSR_SMALL", 0)
+    pkg.set_tuning("CSR_INLINE", 1)
+    pkg.set_csrmm_segment(256)
+    yield 256
+    pkg.set_csrmm_segment(0)
+    pkg.set_tuning("CSR_SMALL", None)
+    pkg.set_tuning("CSR_INLINE", None)
+
+
+def hub_matrix(seed, m=6000, k=9000, avg=8):
+    rng = np.random.default_rng(seed)
+    hubs = {0: 257, 1: 256, 17: 5000, 18: 3000, 19: 700, 1000: 8999, 2500: 513, 2501: 512, 2502: 511,
+            m - 1: 4000, m - 2: 300}
+    for r in rng.choice(np.arange(3000, m - 10), size=25, replace=False):
+        hubs[int(r)] = int(rng.integers(257, 2500))
+    return rng, random_csr(rng, m, k, avg, hubs=hubs, empty_rows={5, 6, 7, 2503, m - 3})
+
+
+@pytest.mark.parametrize("K", [32, 64, 128, 256, 384, 512])
+def test_stream_kernel_inline_segments_vs_oracle(pkg, oracle, forced_stream, K):
+    rng, (rp, ci, v) = hub_matrix(K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C = torch.full((m, K), float("nan"), device="cuda")
+    drp, dci, dv, dB = dev(rp), dev(ci), dev(v), dev(B)
+    pkg.csrmm(drp, dci, dv, dB, C, m, k, K)
+    got = C.cpu().numpy()
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    assert err_vs(oracle, got, ref, rp, ci, v, B, K) <= TOL_FP32
+    seq = oracle.csrmm_f32_seq(rp, ci, v, B, K)
+    short = np.diff(rp) <= forced_stream
+    assert np.array_equal(got[short], seq[short])
+    assert np.all(got[[5, 6, 7, 2503, m - 3]] == 0)
+    # determinism: who computes which segment changes from launch to launch, the bits must not
+    for _ in range(3):
+        C2 = torch.full((m, K), float("nan"), device="cuda")
+        pkg.csrmm(drp, dci, dv, dB, C2, m, k, K)
+        assert torch.equal(C, C2)
+    # nnz unknown to the callee (gespmm_csrmm's signature)
+    C3 = torch.full((m, K), float("nan"), device="cuda")
+    pkg.gespmm_csrmm(m, K, drp, dci, dv, dB, C3)
+    assert torch.equal(C, C3)
+
+
+@pytest.mark.parametrize("K", [64, 256, 384, 512])
+@pytest.mark.parametrize("alpha,beta", [(0.5, -2.0), (2.0, 1.0)])
+def test_stream_kernel_inline_segments_alpha_beta(pkg, oracle, forced_stream, K, alpha, beta):
+    rng, (rp, ci, v) = hub_matrix(100 + K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    C = dev(C0)
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, k, K, alpha=alpha, beta=beta)
+    ref = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=alpha, beta=beta)
+    assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K, alpha, beta, C0) <= TOL_FP32
+
+
+@pytest.mark.parametrize("K", [128, 256, 512])
+def test_stream_kernel_understated_nnz_void_tickets(pkg, oracle, forced_stream, K):
+    """A caller that understates nnz gets a queue too small for its hub rows: rows that do not fit publish void
+    tickets and are computed in place by the warp that met them."""
+    rng, (rp, ci, v) = hub_matrix(200 + K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    ref = oracle.csrmm(rp, ci, v, B, K)
+    for nnz in (256, 3000, 20000):
+        C = torch.full((m, K), float("nan"), device="cuda")
+        pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, k, K, nnz=nnz)
+        assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32, nnz
+
+
+@pytest.mark.parametrize("K", [128, 256])
+def test_stream_kernel_shards_concatenate_bit_for_bit(pkg, oracle, forced_stream, K):
+    """8 nnz-balanced row ranges, each run as its own call with rebased rowptr and the whole
+    matrix's segment length, concatenate to the single-call result bit for bit."""
+    from spmm_denseblock_b200 import shard
+    rng, (rp, ci, v) = hub_matrix(300 + K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    dB = dev(B)
+    full = torch.empty(m, K, device="cuda")
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dB, full, m, k, K)
+    ranges = shard.shard_plan(torch.from_numpy(rp), 8)
+    assert ranges[0][0] == 0 and ranges[-1][1] == m
+    for lo, hi in ranges:
+        rps = (rp[lo:hi + 1] - rp[lo]).astype(np.int32)
+        cis, vs = ci[rp[lo]:rp[hi]], v[rp[lo]:rp[hi]]
+        part = torch.full((hi - lo, K), float("nan"), device="cuda")
+        pkg.csrmm(dev(rps), dev(cis), dev(vs), dB, part, hi - lo, k, K)
+        assert torch.equal(part, full[lo:hi]), (lo, hi)
+
+
+def test_stream_kernel_two_streams_in_flight(pkg, oracle, forced_stream):
+    """Library scratch is per (device, stream): two calls on two streams in flight together do not share the
+    long-row queue."""
+    K = 256
+    rng, (rp, ci, v) = hub_matrix(7)
+    rng2, (rp2, ci2, v2) = hub_matrix(8, m=5000, k=9000, avg=6)
+    m, m2, k = rp.size - 1, rp2.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    dB = dev(B)
+    a = [dev(x) for x in (rp, ci, v)]
+    b = [dev(x) for x in (rp2, ci2, v2)]
+    ref1 = torch.empty(m, K, device="cuda")
+    ref2 = torch.empty(m2, K, device="cuda")
+    pkg.csrmm(*a, dB, ref1, m, k, K)
+    pkg.csrmm(*b, dB, ref2, m2, k, K)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    outs = []
+    for it in range(6):
+        c1 = torch.full((m, K), float("nan"), device="cuda")
+        c2 = torch.full((m2, K), float("nan"), device="cuda")
+        torch.cuda.synchronize()
+        with torch.cuda.stream(s1):
+            pkg.csrmm(*a, dB, c1, m, k, K)
+        with torch.cuda.stream(s2):
+            pkg.csrmm(*b, dB, c2, m2, k, K)
+        outs.append((c1, c2))
+    torch.cuda.synchronize()
+    for c1, c2 in outs:
+        assert torch.equal(c1, ref1) and torch.equal(c2, ref2)
+
+
+# ----------------------------------------------------------------------------- config-shaped inputs, natural dispatch
+def _config_case(name, scale, K, seed=1234, **over):
+    from spmm_denseblock_b200 import graphs
+    rp, ci = graphs.make_config_graph(name, device="cuda", scale=scale, seed=seed, **over)
+    n = rp.numel() - 1
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    B = torch.rand(n, K, generator=g, device="cuda") * 2 - 1
+    val = torch.rand(ci.numel(), generator=g, device="cuda") * 2 - 1
+    return rp, ci, val, B, n
+
+
+@pytest.mark.parametrize("name,scale,K,over", [
+    ("c2_arxiv", 1.0, 128, {}),                      # small-matrix path (pipe kernel + side stream)
+    ("c4_molhiv", 1.0, 300, {}),                     # stream kernel VEC 3, 64-entry segments
+    ("c5_products", 0.1, 256, {}),                   # stream kernel VEC 2 with inline segments at its natural size
+    ("c5_products", 0.1, 256, dict(p_local=0.9, window=4096)),
+    ("c5_products", 0.1, 512, {}),                   # VEC 4
+    ("c5_products", 0.1, 128, {}),                   # VEC 1
+    ("c3_proteins", 0.25, 128, {}),                  # rows kernel (271 nnz per row)
+])
+def test_csrmm_config_shapes_vs_oracle(pkg, oracle, name, scale, K, over):
+    rp, ci, val, B, n = _config_case(name, scale, K, **over)
+    C = torch.full((n, K), float("nan"), device="cuda")
+    pkg.csrmm(rp, ci, val, B, C, n, n, K)
+    C2 = torch.full((n, K), float("nan"), device="cuda")
+    pkg.gespmm_csrmm(n, K, rp, ci, val, B, C2)
+    assert torch.equal(C, C2)
+    h = [t.cpu().numpy() for t in (rp, ci, val, B)]
+    ref = oracle.csrmm(*h, K)
+    got = C.cpu().numpy()
+    assert err_vs(oracle, got, ref, *h, K) <= TOL_FP32
+    seq = oracle.csrmm_f32_seq(*h, K)
+    short = np.diff(h[0]) <= pkg.csrmm_segment(ci.numel(), m=n)
+    assert short.sum() > 0 and np.array_equal(got[short], seq[short])
+    if name == "c5_products":
+        assert ci.numel() >= 4 << 20 and (~short).sum() > 0  # inline-segment path with queued hub rows
+
+
+def test_csrmm_column_major_c_beyond_65535_row_tiles(pkg, oracle):
+    """cuSPARSE-layout call (column-major C, run_csrmm.cu:133-142) with more than 65 535 * 32 rows: the
+    transposing epilogue must not put the row tiles on grid.y."""
+    m, k, K = 2_200_000, 1000, 4
+    rng = np.random.default_rng(5)
+    rp = np.arange(m + 1, dtype=np.int32)  # one entry per row
+    ci = rng.integers(0, k, m).astype(np.int32)
+    v = rng.uniform(-1, 1, m).astype(np.float32)
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C = torch.full((K, m), float("nan"), device="cuda")
+    pkg.csrmm(dev(rp), dev(ci), dev(v), dev(B), C, m, k, K, c_layout=pkg.COL_MAJOR)
+    ref = (v[:, None] * B[ci]).astype(np.float32)
+    assert np.array_equal(C.cpu().numpy().T, ref)
+
+
+def test_tuning_knobs_roundtrip(pkg):
+    assert pkg.get_tuning("NO_SUCH_KNOB", 7) == 7
+    pkg.set_tuning("NO_SUCH_KNOB", 3)
+    assert pkg.get_tuning("NO_SUCH_KNOB", 7) == 3
+    pkg.set_tuning("NO_SUCH_KNOB", None)
+    assert pkg.get_tuning("NO_SUCH_KNOB", 7) == 7
