@@ -92,6 +92,32 @@ int spmmdb_csrmm_f32(int m, int k, int K, int64_t nnz, const int* rowptr, const 
                      const float* val, const float* B, int64_t ldb, int b_layout, float* C,
                      int64_t ldc, int c_layout, float alpha, float beta, void* stream);
 
+/* --------------------------------------------------------------------------
+ * Extended CSR entry (row-major B and C only): the operand and cache-residency levers BASELINE.json's
+ * north_star names for this bandwidth-bound op, next to the drop-in above.
+ *   b_dtype     SPMMDB_DTYPE_F32, or SPMMDB_DTYPE_BF16: B holds bf16 rows (made once per feature matrix by
+ *               spmmdb_dense_pack_bf16; ldb in elements, a multiple of 8, K % 8 == 0, K <= 1024).  The B-row
+ *               gathers -- nnz * K * 4 bytes through L2, what bounds the op on graphs -- are halved; A's values,
+ *               the accumulation and C stay fp32.  Error against the fp32 result <= 2^-9 relative per
+ *               product (stated tolerance 1e-2, measured ~2e-3 relative to sum |a||b|).
+ *   hot_bitmap  NULL, or k bits from spmmdb_csr_hot_columns: B rows of marked columns are loaded with an L2
+ *               evict_last policy, all others evict_first, so the most re-read rows stay resident instead of
+ *               being flushed by rows that are read once.  Same bits as without it.
+ * spmmdb_csr_hot_columns marks the most frequent columns of `colind`, as many as fit `max_hot_columns`
+ * (e.g. 60 % of the L2 size / bytes per B row); whole frequency classes only, so fewer may be marked.
+ * One pass over colind per graph (0.3 ms for 62 M non-zeros); hot_bitmap holds (k + 31) / 32 words;
+ * n_hot_host (HOST, may be NULL; non-NULL synchronises) receives the number marked.
+ * ------------------------------------------------------------------------ */
+#define SPMMDB_DTYPE_F32 0
+#define SPMMDB_DTYPE_BF16 1
+int spmmdb_csrmm_ex_f32(int m, int k, int K, int64_t nnz, const int* rowptr, const int* colind, const float* val,
+                        const void* B, int b_dtype, int64_t ldb, float* C, int64_t ldc, float alpha, float beta,
+                        const unsigned* hot_bitmap, void* stream);
+int spmmdb_csr_hot_columns(int k, int64_t nnz, const int* colind, int64_t max_hot_columns, unsigned* hot_bitmap,
+                           int* n_hot_host, void* stream);
+int spmmdb_dense_pack_bf16(int64_t rows, int K, const float* in, int64_t ldi, void* out_bf16, int64_t ldo,
+                           void* stream);
+
 /* Row-segment length: rows of at most this many non-zeros are one sequential FMA chain.
  *   spmmdb_csrmm_segment(nnz)         lower bound that depends on nnz alone (64 / 256 / 512)
  *   spmmdb_csrmm_segment_for(m, nnz)  the length a call with these sizes uses: the above, raised to

@@ -20,6 +20,10 @@ STATUS = {0: "OK", -1: "INVALID_VALUE", -2: "NOT_SUPPORTED", -3: "CUDA", -4: "AL
 SIGNATURES = {
     "spmmdb_csrmm_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, c_i64, C.c_int, vp, c_i64, C.c_int,
                          C.c_float, C.c_float, vp],
+    "spmmdb_csrmm_ex_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, C.c_int, c_i64, vp, c_i64, C.c_float,
+                            C.c_float, vp, vp],
+    "spmmdb_csr_hot_columns": [C.c_int, c_i64, vp, c_i64, vp, C.POINTER(C.c_int), vp],
+    "spmmdb_dense_pack_bf16": [c_i64, C.c_int, vp, c_i64, vp, c_i64, vp],
     "spmmdb_csrmm_segment": [c_i64],
     "spmmdb_csrmm_segment_for": [C.c_int, c_i64],
     "spmmdb_set_csrmm_segment": [C.c_int],

@@ -5,7 +5,8 @@
 namespace spmmdb {
 
 int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* colind, const float* val,
-                   const float* B, int64_t ldb, float* C, int64_t ldc, float alpha, float beta, cudaStream_t st);
+                   const float* B, int64_t ldb, float* C, int64_t ldc, float alpha, float beta, cudaStream_t st,
+                   int b_bf16 = 0, const unsigned* hot = nullptr);
 int bsrmm_simt(int dir, int trans_b, int mb, int n, int bs, float alpha, const float* val, const int* rowptr,
                const int* colind, const float* B, int64_t ldb, float beta, float* C, int64_t ldc, int c_layout,
                cudaStream_t st);

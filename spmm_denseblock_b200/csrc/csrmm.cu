@@ -34,8 +34,11 @@ struct CsrArgs {
   const int* rowptr;
   const int* colind;
   const float* val;
-  const float* B;
-  int64_t ldb;
+  const float* B;       // fp32 rows, or (b_bf16) bf16 rows behind the same pointer
+  int64_t ldb;          // in elements of B
+  int b_bf16;           // stream kernel only: B holds bf16 (8 columns per 16-byte vector)
+  const unsigned* hot;  // stream kernel only: bitmap of the columns whose B rows should stay in L2 (or null)
+  int cold_policy;      // L2 eviction class of the other rows: 0 normal, 1 evict_first, 2 evict_unchanged
   float* C;
   int64_t ldc;
   float alpha, beta;
@@ -506,18 +509,93 @@ __device__ __forceinline__ int publish_long_row(const CsrArgs& a, int row, int l
 // result does not depend on who computed what.  The kernel is launched twice:
 // the second launch finds the item counter exhausted and only sweeps segments
 // queued after a warp's last look at the queue.
-template <int VEC, int U, int MINB>
+// How the stream kernel reads a 16-byte vector of a B row and multiplies it in.
+//   fp32 B: 4 columns per vector (one float4 of accumulators), bf16 B: 8 columns (two float4).
+// HINT: the load carries an L2 eviction policy (createpolicy): evict_last for the rows of "hot" columns
+// (those the plan marked to stay resident), the caller's choice for the rest.
+template <bool BF16> struct BVec;
+template <> struct BVec<false> {
+  using Raw = float4;
+  static constexpr int OV = 1;  // float4 accumulators per raw vector
+  __device__ static void fma(float4 (&acc)[1], float v, const Raw& b) { VecOps<float4>::fma(acc[0], v, b); }
+};
+template <> struct BVec<true> {
+  using Raw = uint4;
+  static constexpr int OV = 2;
+  __device__ static void fma(float4 (&acc)[2], float v, const Raw& b) {
+    // bf16 -> fp32 is a 16-bit shift: element 2j in the low half of word j, element 2j + 1 in the high half
+    acc[0].x = fmaf(v, __uint_as_float(b.x << 16), acc[0].x);
+    acc[0].y = fmaf(v, __uint_as_float(b.x & 0xffff0000u), acc[0].y);
+    acc[0].z = fmaf(v, __uint_as_float(b.y << 16), acc[0].z);
+    acc[0].w = fmaf(v, __uint_as_float(b.y & 0xffff0000u), acc[0].w);
+    acc[1].x = fmaf(v, __uint_as_float(b.z << 16), acc[1].x);
+    acc[1].y = fmaf(v, __uint_as_float(b.z & 0xffff0000u), acc[1].y);
+    acc[1].z = fmaf(v, __uint_as_float(b.w << 16), acc[1].z);
+    acc[1].w = fmaf(v, __uint_as_float(b.w & 0xffff0000u), acc[1].w);
+  }
+};
+__device__ __forceinline__ float4 ldg_raw(const float4* p) { return __ldg(p); }
+__device__ __forceinline__ uint4 ldg_raw(const uint4* p) { return __ldg(p); }
+__device__ __forceinline__ float4 ldg_policy(const float4* p, uint64_t pol) {
+  float4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ uint4 ldg_policy(const uint4* p, uint64_t pol) {
+  uint4 r;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 0f3F800000;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 0f3F800000;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_normal() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 0f3F800000;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_unchanged() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_unchanged.b64 %0, 0f3F800000;" : "=l"(p));
+  return p;
+}
+
+template <int VEC, int U, int MINB, bool BF16, bool HINT>
 __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a) {
   using Ops = VecOps<float4>;
+  using BV = BVec<BF16>;
+  using Raw = typename BV::Raw;
+  constexpr int OV = BV::OV;
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const int nvec = a.K >> 2;
+  const int nvec = a.K / (4 * OV);  // 16-byte vectors per row of B
   const int nitems = (a.m + a.rpi - 1) / a.rpi;
-  const float4* __restrict__ Bv = reinterpret_cast<const float4*>(a.B) + lane;
-  const int64_t ldbv = a.ldb >> 2;
+  const Raw* __restrict__ Bv = reinterpret_cast<const Raw*>(a.B) + lane;
+  const int64_t ldbv = a.ldb / (4 * OV);
+  const int kpadv = a.Kpad >> 2;
   bool colok[VEC];
 #pragma unroll
   for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
+  uint64_t pol_hot = 0, pol_cold = 0;
+  if (HINT) {
+    pol_hot = policy_evict_last();
+    pol_cold = a.cold_policy == 1 ? policy_evict_first() : (a.cold_policy == 2 ? policy_evict_unchanged() : policy_evict_normal());
+  }
+  // (column, value) chunk loads; with HINT the column's bit of the hot bitmap rides in the sign bit
+  auto load_cv = [&](int idx, int& c, float& v) {
+    c = __ldg(a.colind + idx);
+    v = __ldg(a.val + idx);
+    if (HINT) c |= (int)(((__ldg(a.hot + (c >> 5)) >> (c & 31)) & 1u) << 31);
+  };
 
   int item = 0;
   if (lane == 0) item = atomicAdd(a.counters + 3, 1);
@@ -536,7 +614,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
     pending = 0;
     int next_item = item;
     int nrows = 1, s = 0, e = 0, lng = 0;
-    float4* __restrict__ obase;  // output row 0 of this work unit (this lane's first column)
+    float4* __restrict__ obase;  // output row 0 of this work unit
     int ldo;
     if (t >= 0) {
       volatile unsigned long long* pe = a.seg_entry + t;
@@ -551,7 +629,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
         e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
       }
       // partial sums are stored raw; alpha / beta are applied by the final add
-      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * (a.Kpad >> 2) + lane;
+      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
       ldo = 0;
     } else {
       if (item >= nitems) break;
@@ -572,7 +650,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
         if (lng) lng = publish_long_row(a, r0 + lane, e - s);
       }
       ldo = (int)(a.ldc >> 2);
-      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo + lane;
+      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
     }
     const int S = __shfl_sync(FULL, s, 0);
     const int E = __shfl_sync(FULL, e, nrows - 1);
@@ -581,9 +659,11 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
     int cr = 0;
     int ce = __shfl_sync(FULL, e, 0);
     int cl = __shfl_sync(FULL, lng, 0);
-    float4 acc[VEC];
+    float4 acc[VEC][OV];
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+    for (int i = 0; i < VEC; ++i)
+#pragma unroll
+      for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
 
     auto flush_advance = [&]() {
       if (!cl) {
@@ -591,17 +671,23 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
           if (colok[i]) {
-            float4 out;
-            if (t >= 0) out = acc[i];
-            else if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[32 * i]);
-            else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i]);
-            else out = acc[i];
-            __stcs(Cv + 32 * i, out);
+#pragma unroll
+            for (int h = 0; h < OV; ++h) {
+              float4* o = Cv + OV * (lane + 32 * i) + h;
+              float4 out;
+              if (t >= 0) out = acc[i][h];
+              else if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+              else out = acc[i][h];
+              __stcs(o, out);
+            }
           }
         }
       }
 #pragma unroll
-      for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
+      for (int i = 0; i < VEC; ++i)
+#pragma unroll
+        for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
       ++cr;
       const int src = min(cr, 31);
       ce = __shfl_sync(FULL, e, src);
@@ -615,30 +701,39 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
     float v = 0.f;
     {
       const int idx = p0 + lane;
-      if (idx >= S && idx < E) { c = __ldg(a.colind + idx); v = __ldg(a.val + idx); }
+      if (idx >= S && idx < E) load_cv(idx, c, v);
     }
     while (p0 < E) {
       int c_n = 0;
       float v_n = 0.f;
       {
         const int idx = p0 + 32 + lane;
-        if (idx < E) { c_n = __ldg(a.colind + idx); v_n = __ldg(a.val + idx); }
+        if (idx < E) load_cv(idx, c_n, v_n);
       }
       const int qhi = min(p0 + 32, E);
 #pragma unroll 1
       for (int kk = (qn - p0) / U * U; p0 + kk < qhi; kk += U) {
-        float4 b[U][VEC];
+        Raw b[U][VEC];
         float vv[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const int cc = __shfl_sync(FULL, c, kk + u);
+          int cc = __shfl_sync(FULL, c, kk + u);
           vv[u] = __shfl_sync(FULL, v, kk + u);
           const int q = p0 + kk + u;
           if (q >= qn && q < qhi) {
-            const float4* __restrict__ brow = Bv + (int64_t)cc * ldbv;
+            if (HINT) {
+              const uint64_t pol = cc < 0 ? pol_hot : pol_cold;
+              cc &= 0x7fffffff;
+              const Raw* __restrict__ brow = Bv + (int64_t)cc * ldbv;
 #pragma unroll
-            for (int i = 0; i < VEC; ++i)
-              if (colok[i]) b[u][i] = __ldg(brow + 32 * i);
+              for (int i = 0; i < VEC; ++i)
+                if (colok[i]) b[u][i] = ldg_policy(brow + 32 * i, pol);
+            } else {
+              const Raw* __restrict__ brow = Bv + (int64_t)cc * ldbv;
+#pragma unroll
+              for (int i = 0; i < VEC; ++i)
+                if (colok[i]) b[u][i] = ldg_raw(brow + 32 * i);
+            }
           }
         }
         const int q0 = p0 + kk;
@@ -648,7 +743,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
           for (int u = 0; u < U; ++u)
 #pragma unroll
             for (int i = 0; i < VEC; ++i)
-              if (colok[i]) Ops::fma(acc[i], vv[u], b[u][i]);
+              if (colok[i]) BV::fma(acc[i], vv[u], b[u][i]);
         } else {
 #pragma unroll
           for (int u = 0; u < U; ++u) {
@@ -658,7 +753,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
               if (!cl) {
 #pragma unroll
                 for (int i = 0; i < VEC; ++i)
-                  if (colok[i]) Ops::fma(acc[i], vv[u], b[u][i]);
+                  if (colok[i]) BV::fma(acc[i], vv[u], b[u][i]);
               }
             }
           }
@@ -678,7 +773,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
             p0 = np0;
             const int idx = p0 + lane;
             c = 0; v = 0.f;
-            if (idx >= qn && idx < E) { c = __ldg(a.colind + idx); v = __ldg(a.val + idx); }
+            if (idx >= qn && idx < E) load_cv(idx, c, v);
           }
         }
       }
@@ -698,15 +793,32 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
       if (last) {
         __threadfence();
         if (lane == 0) a.done[seg_slot] = 0;
-        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * (a.Kpad >> 2) + lane;
-        for (int q = 0; q < seg_nseg; ++q, p += (a.Kpad >> 2)) {
+        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
+        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
 #pragma unroll
           for (int i = 0; i < VEC; ++i)
             if (colok[i]) {
-              if (q == 0) acc[i] = __ldcg(p + 32 * i); else Ops::add(acc[i], __ldcg(p + 32 * i));
+#pragma unroll
+              for (int h = 0; h < OV; ++h) {
+                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
+                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
+              }
             }
         }
-        store_row<float4, 32, VEC>(a, r0, lane, 0, nvec, acc);
+        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+          if (colok[i]) {
+#pragma unroll
+            for (int h = 0; h < OV; ++h) {
+              float4* o = Cv + OV * (lane + 32 * i) + h;
+              float4 out;
+              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+              else out = acc[i][h];
+              __stcs(o, out);
+            }
+          }
       }
     } else {
       item = __shfl_sync(FULL, next_item, 0);
@@ -894,12 +1006,19 @@ int launch_async(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
   return launch_long<float4, 32, VEC, 8>(a, long_ctas, st);
 }
 
-template <int VEC, int U, int MINB>
+template <int VEC, int U, int MINB, bool BF16 = false>
 int launch_stream(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
-  csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);
+  auto kernel = a.hot != nullptr ? csrmm_stream_kernel<VEC, U, MINB, BF16, true> : csrmm_stream_kernel<VEC, U, MINB, BF16, false>;
+  kernel<<<nsm * MINB, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  if (!a.inline_segs) return launch_long<float4, 32, VEC, (VEC >= 3 ? 4 : 8)>(a, long_ctas, st);
-  csrmm_stream_kernel<VEC, U, MINB><<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
+  if (!a.inline_segs) {
+    if (BF16) {  // the long-row kernel reads fp32 B only: queued segments are always taken inline with bf16 B
+      set_last_error("csrmm bf16-B without inline segments", cudaErrorInvalidValue, __FILE__, __LINE__);
+      return SPMMDB_ERR_CUDA;
+    }
+    return launch_long<float4, 32, VEC, (VEC >= 3 ? 4 : 8)>(a, long_ctas, st);
+  }
+  kernel<<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
 }
@@ -998,16 +1117,19 @@ int dispatch(const CsrArgs& a, int long_ctas, bool two_rows, cudaStream_t st) {
 // Core entry: row-major B and C.
 int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* colind, const float* val,
                    const float* B, int64_t ldb, float* C, int64_t ldc, float alpha, float beta,
-                   cudaStream_t st) {
+                   cudaStream_t st, int b_bf16, const unsigned* hot) {
   CsrArgs a;
   a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
+  a.b_bf16 = b_bf16; a.hot = hot;
+  a.cold_policy = SPMMDB_TUNE("CSR_COLD_POLICY", 1);
   const int seg_override = current_segment_override();
   a.seg = seg_override ? seg_override : spmmdb_csrmm_segment_for(m, nnz);
   // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
   // ~10 dependent L2 round trips, the grid-stride long-row kernel half of that (0.155 vs 0.194 ms on C2).
   const int inline_force = SPMMDB_TUNE("CSR_INLINE", -1);  // -1: automatic
   a.inline_segs = inline_force >= 0 ? (inline_force != 0) : (a.seg >= 256);
+  if (b_bf16) a.inline_segs = 1;  // the separate long-row kernel reads fp32 B only
   a.prequeued = 0;
   a.Kpad = (K + 3) & ~3;
   a.epoch = next_epoch();
@@ -1047,7 +1169,31 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   // small matrices with a 128-wide dense side: the two-rows-per-warp rows kernel (see dispatch)
   const int small_env = SPMMDB_TUNE("CSR_SMALL", 1);
   const bool small_k128 = small_env && vec4 && nnz < ((int64_t)4 << 20) && K > 32 && K <= 256 && !dense_rows;
-  if (vec4 && K >= stream_min_k && K <= 512 && !dense_rows && !small_k128) {
+  if (b_bf16) {
+    // bf16-stored B (fp32 accumulate): the stream kernel with 8 columns per 16-byte vector, whatever the shape
+    const bool ok = (K % 8 == 0) && K <= 1024 && (ldb % 8 == 0) && (ldc % 4 == 0) && (((uintptr_t)B | (uintptr_t)C) % 16 == 0);
+    if (!ok) return SPMMDB_ERR_NOT_SUPPORTED;
+    const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;
+    int rpi = 8;
+    while (rpi > 1 && rpi * avg > 512) rpi >>= 1;
+    const int rpi_env = SPMMDB_TUNE("CSR_RPI", 0);
+    if (rpi_env > 0) rpi = rpi_env < 32 ? rpi_env : 32;
+    a.rpi = rpi;
+    const int vec = (K / 8 + 31) / 32;
+    const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
+    if (vec == 1) {
+      if (variant == 1) return launch_stream<1, 8, 3, true>(a, nsm, long_ctas, st);
+      if (variant == 2) return launch_stream<1, 16, 3, true>(a, nsm, long_ctas, st);
+      if (variant == 3) return launch_stream<1, 8, 4, true>(a, nsm, long_ctas, st);
+      return launch_stream<1, 16, 2, true>(a, nsm, long_ctas, st);
+    }
+    if (vec == 2) return launch_stream<2, 8, 2, true>(a, nsm, long_ctas, st);
+    if (vec == 3) return launch_stream<3, 3, 3, true>(a, nsm, long_ctas, st);
+    return launch_stream<4, 2, 3, true>(a, nsm, long_ctas, st);
+  }
+  if (hot != nullptr && !(vec4 && K >= 32 && K <= 512)) a.hot = nullptr;  // the hint is a stream-kernel feature
+  const bool force_stream = a.hot != nullptr;  // a caller that supplies a plan wants the kernel that honours it
+  if (vec4 && K >= stream_min_k && K <= 512 && ((!dense_rows && !small_k128) || force_stream)) {
     // rows per item: measured on B200 (profiles/r1b_csr_rpi_sweep.txt): 8 rows is the best or within 3% of it
     // for avg degree 2 (C4), 6.5 (C2) and 24 (C5); fewer rows per item for denser rows.
     const int64_t avg = m > 0 ? (nnz + m - 1) / m : 1;

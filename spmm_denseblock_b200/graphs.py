@@ -20,10 +20,22 @@ def _gen(seed, device):
     return g
 
 
-def _csr_from_pairs(rows, cols, n_rows, n_cols):
-    """Sort (row, col) pairs, drop duplicates, build int32 CSR."""
+def _csr_from_pairs(rows, cols, n_rows, n_cols, target=None, draw=None, g=None):
+    """Sort (row, col) pairs, drop duplicates, build int32 CSR.  With `target` and `draw` (a function
+    e -> (rows, cols) of e more edges from the same distribution) the de-duplicated edge set is topped up
+    to exactly `target` entries, so a config's stated nnz is met, not undershot by the duplicates."""
     key = rows.to(torch.int64) * n_cols + cols.to(torch.int64)
     key = torch.unique(key)  # sorted + de-duplicated
+    if target is not None and draw is not None:
+        for _ in range(12):
+            short = target - key.numel()
+            if short <= 0:
+                break
+            r2, c2 = draw(int(short * 1.05) + 1024)
+            key = torch.unique(torch.cat([key, r2.to(torch.int64) * n_cols + c2.to(torch.int64)]))
+        if key.numel() > target:  # drop the surplus uniformly
+            keep = torch.randperm(key.numel(), generator=g, device=key.device)[:target]
+            key = key[torch.sort(keep).values]
     r = torch.div(key, n_cols, rounding_mode="floor")
     c = (key - r * n_cols).to(torch.int32)
     counts = torch.bincount(r, minlength=n_rows)
@@ -80,7 +92,7 @@ def power_law_degrees(n, nnz, max_degree, gamma=2.2, seed=1234, device="cpu"):
     return deg[perm]
 
 
-def power_law_graph(n, nnz, max_degree, gamma=2.2, p_local=0.0, window=2048, seed=1234, device="cpu"):
+def power_law_graph(n, nnz, max_degree, gamma=2.2, p_local=0.0, window=2048, seed=1234, device="cpu", exact=True):
     """C2 / C5: power-law out-degrees; each edge's column is, with probability
     p_local, a neighbour id within ~`window` of the row (the locality a
     community-aware reordering such as Rabbit / Gorder leaves behind), otherwise
@@ -88,20 +100,28 @@ def power_law_graph(n, nnz, max_degree, gamma=2.2, p_local=0.0, window=2048, see
     g = _gen(seed + 1, device)
     deg = power_law_degrees(n, nnz, max_degree, gamma, seed, device)
     rows = torch.arange(n, device=device).repeat_interleave(deg)
-    e = rows.numel()
     cdf = torch.cumsum(deg.to(torch.float64), 0)
-    u = torch.rand(e, generator=g, device=device, dtype=torch.float64) * cdf[-1]
-    cols = torch.searchsorted(cdf, u).clamp_(max=n - 1)
-    if p_local > 0:
-        local = torch.rand(e, generator=g, device=device) < p_local
-        off = torch.round(torch.randn(e, generator=g, device=device) * (window / 2.0)).to(torch.int64)
-        lc = torch.remainder(rows + off, n)
-        cols = torch.where(local, lc, cols)
-    return _csr_from_pairs(rows, cols, n, n)
+
+    def columns(rows):
+        e = rows.numel()
+        u = torch.rand(e, generator=g, device=device, dtype=torch.float64) * cdf[-1]
+        cols = torch.searchsorted(cdf, u).clamp_(max=n - 1)
+        if p_local > 0:
+            local = torch.rand(e, generator=g, device=device) < p_local
+            off = torch.round(torch.randn(e, generator=g, device=device) * (window / 2.0)).to(torch.int64)
+            cols = torch.where(local, torch.remainder(rows + off, n), cols)
+        return cols
+
+    def draw(e):  # e more edges: source rows in proportion to their degree, columns as above
+        u = torch.rand(e, generator=g, device=device, dtype=torch.float64) * cdf[-1]
+        r = torch.searchsorted(cdf, u).clamp_(max=n - 1)
+        return r, columns(r)
+
+    return _csr_from_pairs(rows, columns(rows), n, n, target=nnz if exact else None, draw=draw, g=g)
 
 
 def planted_community_graph(n, nnz, min_size=256, max_size=2048, p_in=0.9, shuffle=False, seed=1234,
-                            device="cpu"):
+                            device="cpu", exact=True):
     """C3: stochastic-block-model-like graph: contiguous communities of random size,
     a fraction p_in of every row's edges stays inside its community.  With
     shuffle=True node ids are randomly permuted (what a reordering has to undo);
@@ -120,17 +140,22 @@ def planted_community_graph(n, nnz, min_size=256, max_size=2048, p_in=0.9, shuff
     comm = torch.arange(sizes.numel(), device=device).repeat_interleave(sizes)
     deg = max(1, nnz // n)
     rows = torch.arange(n, device=device).repeat_interleave(deg)
-    e = rows.numel()
-    inside = torch.rand(e, generator=g, device=device) < p_in
-    u = torch.rand(e, generator=g, device=device, dtype=torch.float64)
-    c_in = starts[comm[rows]] + torch.floor(u * sizes[comm[rows]].to(torch.float64)).to(torch.int64)
-    c_out = torch.floor(u * n).to(torch.int64)
-    cols = torch.where(inside, c_in, c_out).clamp_(max=n - 1)
-    perm = None
-    if shuffle:
-        perm = torch.randperm(n, generator=g, device=device)
-        rows, cols = perm[rows], perm[cols]
-    rp, ci = _csr_from_pairs(rows, cols, n, n)
+    perm = torch.randperm(n, generator=g, device=device) if shuffle else None
+
+    def columns(rows):
+        e = rows.numel()
+        inside = torch.rand(e, generator=g, device=device) < p_in
+        u = torch.rand(e, generator=g, device=device, dtype=torch.float64)
+        c_in = starts[comm[rows]] + torch.floor(u * sizes[comm[rows]].to(torch.float64)).to(torch.int64)
+        c_out = torch.floor(u * n).to(torch.int64)
+        cols = torch.where(inside, c_in, c_out).clamp_(max=n - 1)
+        return (perm[rows], perm[cols]) if shuffle else (rows, cols)
+
+    def draw(e):
+        return columns(torch.randint(0, n, (e,), generator=g, device=device))
+
+    r0, c0 = columns(rows)
+    rp, ci = _csr_from_pairs(r0, c0, n, n, target=nnz if exact else None, draw=draw, g=g)
     return rp, ci, perm
 
 
@@ -201,13 +226,13 @@ def make_config_graph(name, device="cpu", seed=1234, scale=1.0, **overrides):
         nnz = max(n, int(cfg["nnz"] * scale))
         md = max(8, min(cfg["max_degree"], n // 2))
         return power_law_graph(n, nnz, md, p_local=cfg.get("p_local", 0.0), window=cfg.get("window", 2048),
-                               seed=seed, device=device)
+                               seed=seed, device=device, exact=cfg.get("exact", True))
     if kind == "community":
         n = max(1024, int(cfg["n"] * scale))
         nnz = max(n, int(cfg["nnz"] * scale))
         rp, ci, _ = planted_community_graph(n, nnz, shuffle=cfg.get("shuffle", False), seed=seed, device=device,
                                             min_size=cfg.get("min_size", 256), max_size=cfg.get("max_size", 2048),
-                                            p_in=cfg.get("p_in", 0.9))
+                                            p_in=cfg.get("p_in", 0.9), exact=cfg.get("exact", True))
         return rp, ci
     if kind == "molecules":
         rp, ci, _ = molecule_batch_graph(max(2, int(cfg["num_graphs"] * scale)), seed=seed, device=device)

@@ -69,6 +69,38 @@ def csrmm(rowptr, colind, val, B, C_out, m, k, K, ldb=None, b_layout=ROW_MAJOR, 
     return C_out
 
 
+def csr_hot_columns(k, colind, max_hot_columns):
+    """Bitmap (int32 words) of the most frequent columns that fit max_hot_columns, and how many were marked."""
+    _dev(colind)
+    bitmap = torch.zeros((k + 31) // 32, dtype=torch.int32, device=colind.device)
+    n_hot = C.c_int(0)
+    rc = lib().spmmdb_csr_hot_columns(k, colind.numel(), _p(colind), int(max_hot_columns), _p(bitmap), C.byref(n_hot),
+                                      _stream())
+    check(rc, "spmmdb_csr_hot_columns")
+    return bitmap, n_hot.value
+
+
+def dense_pack_bf16(B, K=None):
+    """fp32 [rows, K] -> bf16 [rows, K] (spmmdb_dense_pack_bf16, round to nearest even)."""
+    _dev(B)
+    rows, ld = B.shape
+    K = ld if K is None else K
+    out = torch.empty(rows, K, dtype=torch.bfloat16, device=B.device)
+    check(lib().spmmdb_dense_pack_bf16(rows, K, _p(B), ld, _p(out), K, _stream()), "spmmdb_dense_pack_bf16")
+    return out
+
+
+def csrmm_ex(rowptr, colind, val, B, C_out, m, k, K, ldb=None, ldc=None, alpha=1.0, beta=0.0, hot=None, nnz=None):
+    """spmmdb_csrmm_ex_f32: row-major, B fp32 or bf16 (by tensor dtype), optional hot-column bitmap."""
+    _dev(rowptr, colind, val, B, C_out, hot)
+    dtype = 1 if B.dtype == torch.bfloat16 else 0
+    nnz = colind.numel() if nnz is None else nnz
+    rc = lib().spmmdb_csrmm_ex_f32(m, k, K, nnz, _p(rowptr), _p(colind), _p(val), _p(B), dtype, K if ldb is None else ldb,
+                                   _p(C_out), K if ldc is None else ldc, alpha, beta, _p(hot), _stream())
+    check(rc, "spmmdb_csrmm_ex_f32")
+    return C_out
+
+
 def gespmm_csrmm(A_nrows, B_ncols, A_rowPtr, A_colInd, A_val, B, C_out):
     """gespmm_csrmm<float>(A_nrows, B_ncols, rowPtr, colInd, val, B, C): row-major B/C,
     alpha=1, beta=0, nnz unknown to the callee (gespmm_csrmm.h:422-426)."""

@@ -225,3 +225,73 @@ def test_tuning_knobs_roundtrip(pkg):
     assert pkg.get_tuning("NO_SUCH_KNOB", 7) == 3
     pkg.set_tuning("NO_SUCH_KNOB", None)
     assert pkg.get_tuning("NO_SUCH_KNOB", 7) == 7
+
+
+# ----------------------------------------------------------------------------- extended entry: bf16 B, hot columns
+def _bf16_round(x):
+    return torch.from_numpy(x).to(torch.bfloat16).to(torch.float32).numpy()
+
+
+@pytest.mark.parametrize("K", [64, 128, 256, 512, 1024])
+@pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.5, -2.0)])
+def test_csrmm_ex_bf16_b(pkg, oracle, K, alpha, beta):
+    """B stored as bf16, fp32 accumulate: exactly the fp32 kernel's arithmetic on the rounded B (bit for bit on
+    rows of one segment), and within the stated 1e-2 of the product with the unrounded B."""
+    rng, (rp, ci, v) = hub_matrix(400 + K, m=3000, k=5000)
+    m, k = rp.size - 1, 5000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    Bb = pkg.dense_pack_bf16(dev(B))
+    Br = _bf16_round(B)
+    assert torch.equal(Bb.float().cpu(), torch.from_numpy(Br))  # round to nearest even, like torch
+    C = dev(C0)
+    pkg.csrmm_ex(dev(rp), dev(ci), dev(v), Bb, C, m, k, K, alpha=alpha, beta=beta)
+    got = C.cpu().numpy()
+    ref_r = oracle.csrmm(rp, ci, v, Br, K, C0=C0, alpha=alpha, beta=beta)
+    assert err_vs(oracle, got, ref_r, rp, ci, v, Br, K, alpha, beta, C0) <= TOL_FP32
+    ref = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=alpha, beta=beta)
+    assert err_vs(oracle, got, ref, rp, ci, v, B, K, alpha, beta, C0) <= TOL_BF16B
+    if alpha == 1.0 and beta == 0.0:
+        seq = oracle.csrmm_f32_seq(rp, ci, v, Br, K)
+        short = np.diff(rp) <= pkg.csrmm_segment(ci.size, m=m)
+        assert np.array_equal(got[short], seq[short])
+
+
+def test_csrmm_ex_bf16_b_unsupported_shapes(pkg):
+    z = torch.zeros(8, dtype=torch.int32, device="cuda")
+    Bb = torch.zeros(4, 12, dtype=torch.bfloat16, device="cuda")
+    C = torch.zeros(7, 12, device="cuda")
+    with pytest.raises(pkg.SpmmdbError):
+        pkg.csrmm_ex(z, z[:0], torch.zeros(0, device="cuda"), Bb, C, 7, 4, 12)  # K % 8 != 0
+
+
+@pytest.mark.parametrize("K,bf16", [(256, False), (128, False), (256, True), (512, True)])
+def test_csrmm_ex_hot_columns_same_bits(pkg, oracle, forced_stream, K, bf16):
+    """The hot-column bitmap only changes L2 eviction hints: results are the bits of the plain call."""
+    rng, (rp, ci, v) = hub_matrix(500 + K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    dB = pkg.dense_pack_bf16(dev(B)) if bf16 else dev(B)
+    d = [dev(x) for x in (rp, ci, v)]
+    budget = 700
+    hot, n_hot = pkg.csr_hot_columns(k, d[1], budget)
+    cnt = np.bincount(ci, minlength=k)
+    # whole frequency classes, as many as fit the budget
+    t = max(1, min(x for x in range(1, cnt.max() + 2) if (cnt >= x).sum() <= budget))
+    want = cnt >= t
+    assert n_hot == int(want.sum()) <= budget and n_hot > 0
+    bits = np.unpackbits(hot.cpu().numpy().view(np.uint8), bitorder="little")[:k].astype(bool)
+    assert np.array_equal(bits, want)
+    plain = torch.full((m, K), float("nan"), device="cuda")
+    hinted = torch.full((m, K), float("nan"), device="cuda")
+    pkg.csrmm_ex(*d, dB, plain, m, k, K)
+    for policy in (0, 1, 2):
+        pkg.set_tuning("CSR_COLD_POLICY", policy)
+        try:
+            pkg.csrmm_ex(*d, dB, hinted, m, k, K, hot=hot)
+        finally:
+            pkg.set_tuning("CSR_COLD_POLICY", None)
+        assert torch.equal(plain, hinted), policy
+    if not bf16:
+        ref = oracle.csrmm(rp, ci, v, B, K)
+        assert err_vs(oracle, plain.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32
