@@ -223,13 +223,20 @@ def main():
                     cb = 4 * (n + 1) + 8 * nnz + 4 * (mb + 1) + 4 * nnzb + 4 * nnzb * bs * bs
                     emit(config=key, op="csr2bsr", bs=bs, nnzb=nnzb, fill=nnz / (nnzb * bs * bs), impl="spmmdb_csr2bsr",
                          ms_med=t_ours[0], ms_min=t_ours[1], alg_bytes=cb, hbm_frac=cb / t_ours[0] / 1e6 / peak)
-                    t_v = _time(lambda: cusparse_csr2bsr(n, n, rp, ci, val, bs), warm=1, iters=5, flush=flush)
-                    vrp, vci, vv = cusparse_csr2bsr(n, n, rp, ci, val, bs)
-                    emit(config=key, op="csr2bsr", bs=bs, nnzb=nnzb, impl="cusparseXcsr2bsrNnz + cusparseScsr2bsr",
-                         ms_med=t_v[0], ms_min=t_v[1], alg_bytes=cb, hbm_frac=cb / t_v[0] / 1e6 / peak,
-                         bit_equal=bool(torch.equal(vrp, brp) and torch.equal(vci, bci) and torch.equal(vv, bv)))
-                    del vrp, vci, vv
-                    if nnzb * bs * bs * 12 < 20e9:
+                    # cuSPARSE indexes bsr_val with 32-bit ints: nnzb * bs^2 >= 2^31 is an illegal access inside the
+                    # library (seen on C3 bs 32: 4.02 M blocks x 1024), after which the context is gone
+                    fits32 = nnzb * bs * bs < 2 ** 31
+                    if fits32:
+                        t_v = _time(lambda: cusparse_csr2bsr(n, n, rp, ci, val, bs), warm=1, iters=5, flush=flush)
+                        vrp, vci, vv = cusparse_csr2bsr(n, n, rp, ci, val, bs)
+                        emit(config=key, op="csr2bsr", bs=bs, nnzb=nnzb, impl="cusparseXcsr2bsrNnz + cusparseScsr2bsr",
+                             ms_med=t_v[0], ms_min=t_v[1], alg_bytes=cb, hbm_frac=cb / t_v[0] / 1e6 / peak,
+                             bit_equal=bool(torch.equal(vrp, brp) and torch.equal(vci, bci) and torch.equal(vv, bv)))
+                        del vrp, vci, vv
+                    else:
+                        emit(config=key, op="csr2bsr", bs=bs, nnzb=nnzb, impl="cusparseXcsr2bsrNnz + cusparseScsr2bsr",
+                             error="skipped: nnzb * bs^2 >= 2^31 overflows cuSPARSE's 32-bit value index")
+                    if fits32 and nnzb * bs * bs * 12 < 20e9:
                         bb = 4 * (mb + 1) + 4 * nnzb + 4 * nnzb * bs * bs + 4 * (n + 1) + 8 * nnzb * bs * bs
                         t_o = _time(lambda: pkg.bsr2csr(mb, mb, brp, bci, bv, bs), warm=1, iters=5, flush=flush)
                         o = pkg.bsr2csr(mb, mb, brp, bci, bv, bs)
@@ -251,18 +258,21 @@ def main():
                     bbytes = 4 * (mb + 1) + 4 * nnzb + 4 * nnzb * bs * bs + 4 * mp * K + 4 * mp * K
                     bbase = dict(config=key, op="bsrmm", bs=bs, nnzb=nnzb, fill=nnz / (nnzb * bs * bs), K=K,
                                  dense_flops=dense, alg_bytes=bbytes)
-                    med, mn = _time(lambda: cusparse_bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 0.0, Zv,
-                                                           mp), iters=a.iters, flush=flush)
-                    emit(**bbase, impl="cusparseSbsrmm", ms_med=med, ms_min=mn, dense_tflops=dense / med / 1e9,
-                         useful_tflops=2.0 * nnz * K / med / 1e9, hbm_frac=bbytes / med / 1e6 / peak)
+                    if fits32:
+                        med, mn = _time(lambda: cusparse_bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 0.0,
+                                                               Zv, mp), iters=a.iters, flush=flush)
+                        emit(**bbase, impl="cusparseSbsrmm", ms_med=med, ms_min=mn, dense_tflops=dense / med / 1e9,
+                             useful_tflops=2.0 * nnz * K / med / 1e9, hbm_frac=bbytes / med / 1e6 / peak)
+                    else:
+                        pkg.bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 0.0, Zv, mp, math=pkg.MATH_FP32)
                     for math, mname in ((pkg.MATH_FP32, "fp32 CUDA cores"), (pkg.MATH_TF32, "tf32 tcgen05"),
                                         (pkg.MATH_BF16, "bf16 tcgen05")):
                         f = lambda: pkg.bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K, 0.0, Z, mp, math=math)
                         med, mn = _time(f, iters=a.iters, flush=flush)
                         emit(**bbase, impl=f"spmmdb_bsrmm_f32 {mname}", ms_med=med, ms_min=mn,
                              dense_tflops=dense / med / 1e9, useful_tflops=2.0 * nnz * K / med / 1e9,
-                             hbm_frac=bbytes / med / 1e6 / peak, max_rel_diff_vs_cusparse=maxrel(Z, Zv))
-                    if ref_gpu() is not None:
+                             hbm_frac=bbytes / med / 1e6 / peak, max_rel_diff_vs_cusparse_or_fp32=maxrel(Z, Zv))
+                    if ref_gpu() is not None and fits32:
                         Zr = torch.full((K, mp), float("nan"), device="cuda")
                         med, mn = _time(lambda: ref_rocsparse_bsrmm(0, 1, mb, K, mb, nnzb, 1.0, bv, brp, bci, bs, Bp, K,
                                                                     0.0, Zr, mp), iters=a.iters, flush=flush)

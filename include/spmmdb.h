@@ -266,6 +266,36 @@ int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr,
 int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bounds);
 
 /* --------------------------------------------------------------------------
+ * Multi-GPU execution, one process per GPU (BASELINE.json north_star: nnz-balanced row ranges of A, B replicated
+ * by an NCCL all-gather over NVLink, no reduction).  For a square adjacency matrix (m == k): rank g owns rows
+ * [bounds[g], bounds[g+1]) of A, of C and of B (bounds from spmmdb_shard_plan, HOST array of world + 1 entries).
+ * NCCL is loaded at run time (libnccl.so.2; the copy already in the process if there is one); without it these
+ * return SPMMDB_ERR_NOT_SUPPORTED.
+ *   spmmdb_mg_unique_id      128-byte ncclUniqueId made on one rank; the caller hands the bytes to every rank
+ *                            (MPI, torch.distributed, a file ...)
+ *   spmmdb_mg_create         collective: ncclCommInitRank on the current device + the library's streams / events
+ *   spmmdb_mg_create_from_comm  adopt the caller's ncclComm_t instead
+ *   spmmdb_mg_allgather_rows_f32  all-gather-v, in place, of the row ranges of a full-size row-major B: one NCCL
+ *                            group of send / recv pairs (every rank sends to every peer at once)
+ *   spmmdb_sharded_csrmm_f32  C_local = alpha * A_local * B + beta * C_local where every rank passes ITS rows of
+ *                            B (B_local, [rows][ldb]) and its shard of A (rowptr rebased to 0, global column
+ *                            ids).  K is cut into `slabs` feature slabs (0 = default 4); slab s + 1 is gathered
+ *                            on a communication stream while the SpMM of slab s runs on `stream`.  The replica of
+ *                            B lives in library memory (k * K floats per rank, slab-major).  Same bits as the
+ *                            single-GPU call on the whole matrix when every rank has set the whole matrix's segment length
+ *                            (spmmdb_set_csrmm_segment(spmmdb_csrmm_segment_for(m, nnz))).
+ * ------------------------------------------------------------------------ */
+typedef struct spmmdb_mg spmmdb_mg;
+int spmmdb_mg_unique_id(void* id128);
+int spmmdb_mg_create(int rank, int world, const void* id128, spmmdb_mg** out);
+int spmmdb_mg_create_from_comm(void* nccl_comm, int rank, int world, spmmdb_mg** out);
+int spmmdb_mg_destroy(spmmdb_mg* g);
+int spmmdb_mg_allgather_rows_f32(spmmdb_mg* g, float* B, int64_t ldb, int k, const int* bounds, void* stream);
+int spmmdb_sharded_csrmm_f32(spmmdb_mg* g, int k, int K, int64_t nnz_local, const int* rowptr, const int* colind,
+                             const float* val, const float* B_local, int64_t ldb, const int* bounds, float* C,
+                             int64_t ldc, float alpha, float beta, int slabs, void* stream);
+
+/* --------------------------------------------------------------------------
  * Graph files.  HOST functions, no CUDA call.
  *   SPMMDB_GRAPH_TEXT      <path>_indptr.txt + <path>_indices.txt, the reference's cache format
  *                          (dumpCSRToFile / loadCSRFromFile, load_data.cc:125-165): read, and written

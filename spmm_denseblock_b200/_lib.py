@@ -46,6 +46,13 @@ SIGNATURES = {
     "spmmdb_set_bsrmm_math": [C.c_int],
     "spmmdb_get_bsrmm_math": [],
     "spmmdb_shard_plan": [vp, C.c_int, C.c_int, C.c_int, vp],
+    "spmmdb_mg_unique_id": [vp],
+    "spmmdb_mg_create": [C.c_int, C.c_int, vp, C.POINTER(vp)],
+    "spmmdb_mg_create_from_comm": [vp, C.c_int, C.c_int, C.POINTER(vp)],
+    "spmmdb_mg_destroy": [vp],
+    "spmmdb_mg_allgather_rows_f32": [vp, vp, c_i64, C.c_int, vp, vp],
+    "spmmdb_sharded_csrmm_f32": [vp, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, c_i64, vp, vp, c_i64, C.c_float,
+                                 C.c_float, C.c_int, vp],
     "spmmdb_graph_read": [C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(c_i64), C.POINTER(vp), C.POINTER(vp)],
     "spmmdb_graph_write": [C.c_char_p, C.c_int, C.c_int, c_i64, vp, vp],
     "spmmdb_graph_free": [vp],

@@ -51,3 +51,69 @@ def allgather_rows(B, ranges, group=None):
     for w in works:
         w.wait()
     return B
+
+
+class MultiGpu:
+    """spmmdb_mg handle of this rank (one process per GPU): NCCL communicator + the library's communication
+    stream, made collectively.  The 128-byte NCCL id travels over torch.distributed (any backend); everything
+    after that is the C ABI (spmmdb_mg_*, spmmdb_sharded_csrmm_f32)."""
+
+    def __init__(self, rank=None, world=None, group=None):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from ._lib import lib, check
+        self.rank = dist.get_rank(group) if rank is None else rank
+        self.world = dist.get_world_size(group) if world is None else world
+        L = lib()
+        ident = [None]
+        if self.rank == 0:
+            buf = C.create_string_buffer(128)
+            check(L.spmmdb_mg_unique_id(buf), "spmmdb_mg_unique_id")
+            ident[0] = bytes(buf.raw)
+        if self.world > 1:
+            dist.broadcast_object_list(ident, src=0, group=group)
+        self._h = C.c_void_p(0)
+        check(L.spmmdb_mg_create(self.rank, self.world, C.c_char_p(ident[0]), C.byref(self._h)), "spmmdb_mg_create")
+        self._bounds = None
+
+    def _b(self, ranges):
+        import numpy as np
+        b = np.asarray([r[0] for r in ranges] + [ranges[-1][1]], np.int32)
+        self._bounds = b  # keep alive across the asynchronous call
+        return b.ctypes.data
+
+    def allgather_rows(self, B, ranges):
+        """In-place all-gather-v of the row ranges of a full-size row-major B (one NCCL send / recv group)."""
+        import ctypes as C
+
+        import torch
+
+        from ._lib import lib, check
+        check(lib().spmmdb_mg_allgather_rows_f32(self._h, C.c_void_p(B.data_ptr()), B.stride(0), B.shape[0],
+                                                 C.c_void_p(self._b(ranges)),
+                                                 C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "spmmdb_mg_allgather_rows_f32")
+        return B
+
+    def sharded_csrmm(self, rowptr, colind, val, B_local, ranges, C_out, k, K, alpha=1.0, beta=0.0, slabs=0):
+        """This rank's rows of C = A * B, from its shard of A and ITS rows of B (spmmdb_sharded_csrmm_f32)."""
+        import ctypes as C
+
+        import torch
+
+        from ._lib import lib, check
+        p = lambda t: C.c_void_p(t.data_ptr()) if t is not None and t.numel() > 0 else C.c_void_p(0)  # noqa: E731
+        check(lib().spmmdb_sharded_csrmm_f32(self._h, k, K, colind.numel(), p(rowptr), p(colind), p(val), p(B_local),
+                                             B_local.stride(0) if B_local.numel() else K, C.c_void_p(self._b(ranges)),
+                                             p(C_out), C_out.stride(0) if C_out.numel() else K, alpha, beta, slabs,
+                                             C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+              "spmmdb_sharded_csrmm_f32")
+        return C_out
+
+    def close(self):
+        from ._lib import lib
+        if self._h:
+            lib().spmmdb_mg_destroy(self._h)
+            self._h = None

@@ -55,7 +55,7 @@ def hub_matrix(seed, m=6000, k=9000, avg=8):
     rng = np.random.default_rng(seed)
     hubs = {0: 257, 1: 256, 17: 5000, 18: 3000, 19: 700, 1000: 8999, 2500: 513, 2501: 512, 2502: 511,
             m - 1: 4000, m - 2: 300}
-    for r in rng.choice(np.arange(3000, m - 10), size=25, replace=False):
+    for r in rng.choice(np.arange(m // 2, m - 10), size=25, replace=False):
         hubs[int(r)] = int(rng.integers(257, 2500))
     return rng, random_csr(rng, m, k, avg, hubs=hubs, empty_rows={5, 6, 7, 2503, m - 3})
 
@@ -74,7 +74,7 @@ def test_stream_kernel_inline_segments_vs_oracle(pkg, oracle, forced_stream, K):
     seq = oracle.csrmm_f32_seq(rp, ci, v, B, K)
     short = np.diff(rp) <= forced_stream
     assert np.array_equal(got[short], seq[short])
-    assert np.all(got[[5, 6, 7, 2503, m - 3]] == 0)
+    assert np.all(got[[5, 6, 7, 2503, m - 3]] == 0)  # empty rows are written
     # determinism: who computes which segment changes from launch to launch, the bits must not
     for _ in range(3):
         C2 = torch.full((m, K), float("nan"), device="cuda")

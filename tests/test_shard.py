@@ -117,3 +117,67 @@ def test_shards_concatenate_bit_exact_gpu(parts):
                 pkg.set_csrmm_segment(0)
         outs.append(Cs)
     assert torch.equal(torch.cat(outs), full)
+
+
+def _mg_worker(rank, world, port, out):
+    import torch.distributed as dist
+    import spmm_denseblock_b200 as pkg
+    from spmm_denseblock_b200 import shard
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)  # only carries the 128-byte NCCL id
+    rng = np.random.default_rng(31)
+    n, K = 9000, 256
+    rp, ci, v = random_csr(rng, n, n, 10, hubs={7: 5000, 4100: 2500, 8999: 700}, empty_rows=range(50, 70))
+    Bfull = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    rpd, cid, vd, Bd = d(rp), d(ci), d(v), d(Bfull)
+    full = torch.empty(n, K, device="cuda")
+    pkg.csrmm(rpd, cid, vd, Bd, full, n, n, K)
+    ranges = shard.shard_plan(rpd, world)
+    lo, hi = ranges[rank]
+    mg = shard.MultiGpu(rank, world)
+    ok = True
+    # all-gather-v in place
+    Bg = torch.full((n, K), float("nan"), device="cuda")
+    Bg[lo:hi] = Bd[lo:hi]
+    mg.allgather_rows(Bg, ranges)
+    torch.cuda.synchronize()
+    ok &= bool(torch.equal(Bg, Bd))
+    # sharded SpMM from this rank's rows of B, every slab count, twice in a row (replica reuse)
+    rps, cis, vs = shard.shard_csr(rpd, cid, vd, lo, hi)
+    pkg.set_csrmm_segment(pkg.csrmm_segment(ci.size, m=n))
+    for slabs in (1, 2, 4, 0, 4):
+        Cs = torch.full((hi - lo, K), float("nan"), device="cuda")
+        mg.sharded_csrmm(rps, cis, vs, Bd[lo:hi].contiguous(), ranges, Cs, n, K, slabs=slabs)
+        torch.cuda.synchronize()
+        ok &= bool(torch.equal(Cs, full[lo:hi]))
+    pkg.set_csrmm_segment(0)
+    mg.close()
+    res = [None] * world
+    dist.all_gather_object(res, ok)
+    if rank == 0:
+        out.put(all(res))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [1, 2])
+def test_sharded_csrmm_c_entry_nccl(world):
+    """spmmdb_mg_* + spmmdb_sharded_csrmm_f32 (C++ / NCCL): all-gather-v of B in one send / recv group, feature-slab
+    pipeline; each rank's rows are the bits of the single-GPU product.  world = 2 needs two GPUs."""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_mg_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=300)
+        assert p.exitcode == 0
+    assert out.get(timeout=5) is True
