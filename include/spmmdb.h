@@ -238,6 +238,12 @@ int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colind, const fl
 int spmmdb_permute_rows_f32(int rows, int K, const float* in, int64_t ldi, const int* old2new,
                             float* out, int64_t ldo, void* stream);
 int spmmdb_heatmap(int n, const int* rowptr, const int* colind, int block_dim, int* heat, void* stream);
+/* Fill-decile histogram of the non-empty block_dim x block_dim blocks: calculate_block_density_dist
+ * (block_density_dist.cpp:47-86).  dist10_host (HOST, 10 entries): dist[d] = blocks whose fill
+ * (float)(count * 1.0 / bs^2) lands in decile (int)(fill * 10), 10 folded into 9 -- the reference's expression,
+ * bit for bit.  Synchronises `stream`. */
+int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* colind, int block_dim,
+                                int64_t* dist10_host, void* stream);
 
 /* --------------------------------------------------------------------------
  * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all

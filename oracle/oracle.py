@@ -86,12 +86,13 @@ def csrmm_f32_seq(rowptr, colind, val, B, K):
     return out
 
 
-def spmm_cc_csr(indptr, indices, dense):
+def spmm_cc_csr(indptr, indices, dense, out=None):
     """spmm.cc:7-25 restated (double, int64, unit weights)."""
     indptr = np.ascontiguousarray(indptr, np.int64)
     indices = np.ascontiguousarray(indices, np.int64)
     dense = np.ascontiguousarray(dense, np.float64)
-    out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
+    if out is None:
+        out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
     f = lib().oracle_spmm_cc_csr
     f.argtypes = [C.c_int64, C.c_int64, _i64p, _i64p, _f64p, _f64p]
     f(indptr.size - 1, dense.shape[1], indptr, indices, dense, out)
@@ -235,13 +236,15 @@ def ref_host_lib():
     return _ref_host
 
 
-def ref_csr_spmm(indptr, indices, dense, num_cols=None):
-    """The reference's csr_spmm (spmm.cc:7-25) itself: double, int64, unit weights."""
+def ref_csr_spmm(indptr, indices, dense, num_cols=None, out=None):
+    """The reference's csr_spmm (spmm.cc:7-25) itself: double, int64, unit weights.  `out` (float64 [rows, K],
+    fully overwritten) lets a timed caller keep the allocation outside its clock, as spmm.cc:63-72 does."""
     L = ref_spmm_lib()
     indptr = np.ascontiguousarray(indptr, np.int64)
     indices = np.ascontiguousarray(indices, np.int64)
     dense = np.ascontiguousarray(dense, np.float64)
-    out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
+    if out is None:
+        out = np.zeros((indptr.size - 1, dense.shape[1]), np.float64)
     L.ref_csr_spmm.argtypes = [C.c_int64, C.c_int64, C.c_int64, _i64p, _i64p, _f64p, _f64p]
     L.ref_csr_spmm(indptr.size - 1, dense.shape[0] if num_cols is None else num_cols,
                    dense.shape[1], indptr, indices, dense, out)
@@ -265,6 +268,30 @@ def ref_calculate_nnzb(rowptr, colind, bs):
     rowptr, colind = _i32(rowptr), _i32(colind)
     L.ref_calculate_nnzb.argtypes = [C.c_int, _i32p, _i32p, C.c_int]
     return int(L.ref_calculate_nnzb(rowptr.size - 1, rowptr, colind, bs))
+
+
+def block_density_dist(rowptr, colind, bs):
+    """calculate_block_density_dist restated (block_density_dist.cpp:47-86): non-empty blocks per fill decile,
+    decile = (int)((float)(count * 1.0 / bs^2) * 10) with 10 folded into 9."""
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    nb = (n + bs - 1) // bs
+    rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(rowptr))
+    key = (rows // bs) * nb + colind.astype(np.int64) // bs
+    counts = np.unique(key, return_counts=True)[1]
+    occupy = (counts * 1.0 / (bs * bs)).astype(np.float32)
+    ith = np.minimum((occupy * np.float32(10)).astype(np.int64), 9)
+    return np.bincount(ith, minlength=10).astype(np.int64)
+
+
+def ref_block_density_dist(rowptr, colind, bs):
+    """The reference's own calculate_block_density_dist (oracle/_ref/libref_host.so)."""
+    L = ref_host_lib()
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    out = np.zeros(10, np.int64)
+    L.ref_block_density_dist.argtypes = [C.c_int, _i32p, _i32p, C.c_int, _i64p]
+    L.ref_block_density_dist(rowptr.size - 1, rowptr, colind, bs, out)
+    return out
 
 
 def ref_permutate(rowptr, colind, old2new):

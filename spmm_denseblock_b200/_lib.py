@@ -41,6 +41,7 @@ SIGNATURES = {
     "spmmdb_divide_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_float, vp, vp, vp, vp, vp, vp, vp],
     "spmmdb_permute_csr_f32": [C.c_int, vp, vp, vp, vp, vp, vp, vp, vp],
     "spmmdb_permute_rows_f32": [C.c_int, C.c_int, vp, c_i64, vp, vp, c_i64, vp],
+    "spmmdb_block_fill_histogram": [C.c_int, C.c_int, vp, vp, C.c_int, C.POINTER(c_i64), vp],
     "spmmdb_heatmap": [C.c_int, vp, vp, C.c_int, vp, vp],
     "spmmdb_csrmm_host_f32": [C.c_int, C.c_int, C.c_int, c_i64, vp, vp, vp, vp, vp, C.c_float, C.c_float, vp],
     "spmmdb_set_bsrmm_math": [C.c_int],

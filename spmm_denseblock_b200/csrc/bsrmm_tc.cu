@@ -142,6 +142,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 // 61-63 swizzle mode.
 constexpr uint32_t kLayoutSw128 = 2, kLayoutSw64 = 4, kLayoutSw32 = 6, kLayoutSw128B32 = 1;
 
+// Developer timing experiments (skip loads / MMAs, cycle counters, device printf) exist only in builds made with
+// -DSPMMDB_BSR_DEBUG; in the release kernel the flag word is the constant 0 and the branches fold away.
+#ifdef SPMMDB_BSR_DEBUG
+#define SPMMDB_BSR_DBG(a) ((a).dbg)
+#else
+#define SPMMDB_BSR_DBG(a) 0
+#endif
+
 struct TcArgs {
   int mb, n, bs, G, NT, tiles, nchunks, stages;
   int dir, c_layout;
@@ -256,6 +264,8 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
   // stage buffers first (1024-byte aligned for the 128B swizzle), control block after them
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   TcSmemCtl* ctl = (TcSmemCtl*)(smem + (size_t)a.stages * a.stage_bytes);
+  // column-major C: one 32 x 33 float transpose tile per epilogue warp, after the control block
+  float* tbuf_all = (float*)(((uintptr_t)(ctl + 1) + 15) & ~(uintptr_t)15);
   // warp index broadcast from lane 0: the role dispatch below becomes a warp-uniform branch for the compiler,
   // which lets the MMA / TMA operands live in uniform registers
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
@@ -284,7 +294,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
     if (warp == 0 && lane == 0) s_next = atomicAdd(a.counter, 1);
     const uint32_t smem_base = smem_u32(smem);
     long long dbg_wait = 0, dbg_steps = 0;
-    const long long dbg_t0 = clock64();
+    const long long dbg_t0 = SPMMDB_BSR_DBG(a) ? clock64() : 0;
     while (true) {
       if (warp == 0 && lane == 0) ctl->srow[it & 1] = s_next;
       if (P > 1) named_bar_sync(1, 32 * P); else __syncwarp();
@@ -308,24 +318,24 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
           const uint32_t mask = __shfl_sync(0xffffffffu, rec.y, i);
           const bool mine = (mask >> lane) & 1u;
           if (own == warp) {
-            const long long tw0 = (a.dbg & 32) ? clock64() : 0;
+            const long long tw0 = (SPMMDB_BSR_DBG(a) & 32) ? clock64() : 0;
             mbar_wait(&ctl->empty[stage], phase ^ 1);
-            if (a.dbg & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
+            if (SPMMDB_BSR_DBG(a) & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
             uint64_t* fb = &ctl->full[stage];
             const uint32_t sB = smem_base + (uint32_t)stage * a.stage_bytes;
             if (lane == 0) {
               ctl->meta[stage].mask = mask;
-              mbar_arrive_expect_tx(fb, ((a.dbg & 2) ? 0u : a.nchunks * a.chunk_bytes) +
-                                            ((a.dbg & 1) ? 0u : __popc(mask) * a.block_bytes));
+              mbar_arrive_expect_tx(fb, ((SPMMDB_BSR_DBG(a) & 2) ? 0u : a.nchunks * a.chunk_bytes) +
+                                            ((SPMMDB_BSR_DBG(a) & 1) ? 0u : __popc(mask) * a.block_bytes));
             }
             __syncwarp();
-            if (a.dbg & 2) {
+            if (SPMMDB_BSR_DBG(a) & 2) {
             } else if (a.b_one) {
               if (lane == 0) tma_load_3d_addr(sB, &mapB, 0, j * a.bs, 0, fb);
             } else if (lane < a.nchunks) {
               tma_load_2d_addr(sB + (uint32_t)lane * a.chunk_bytes, &mapB, lane * FC, j * a.bs, fb);
             }
-            if (mine && !(a.dbg & 1)) tma_load_2d_addr(sB + a.stage_b_bytes + (uint32_t)lane * a.block_bytes, &mapA, 0, cur * a.bs, fb);
+            if (mine && !(SPMMDB_BSR_DBG(a) & 1)) tma_load_2d_addr(sB + a.stage_b_bytes + (uint32_t)lane * a.block_bytes, &mapA, 0, cur * a.bs, fb);
           }
           cur += mine ? 1 : 0;
           if (++own == P) own = 0;
@@ -345,7 +355,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       if (++stage == a.stages) { stage = 0; phase ^= 1; }
       if (term) break;
     }
-    if ((a.dbg & 32) && blockIdx.x == 0 && lane == 0)
+    if ((SPMMDB_BSR_DBG(a) & 32) && blockIdx.x == 0 && lane == 0)
       printf("producer %d: total %lld cyc, own steps %lld, wait(empty) %lld cyc\n", warp, clock64() - dbg_t0, dbg_steps,
              dbg_wait);
   } else if (warp == P) {
@@ -362,7 +372,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       const uint32_t rp = (uint32_t)a.bs * ESIZE;  // row pitch of a block in shared memory
       const uint32_t a_layout = rp == 128 ? kLayoutSw128 : (rp == 64 ? kLayoutSw64 : kLayoutSw32);
       // dbg & 64: timing experiment only (wrong results) -- describe the slab as a K-major operand
-      const bool kmaj_exp = (a.dbg & 64) != 0;
+      const bool kmaj_exp = (SPMMDB_BSR_DBG(a) & 64) != 0;
       const uint32_t idesc_base = (1u << 4) | (FMT << 7) | (FMT << 10) | ((kmaj_exp ? 0u : 1u) << 15) |
                                   ((a.dir == SPMMDB_DIR_COLUMN ? 1u : 0u) << 16) | ((128u >> 4) << 24);
       const int ksteps = a.bs / KI;
@@ -383,17 +393,17 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
       const uint32_t smem_base = smem_u32(smem);
       bool done = false;
       long long dbg_wait = 0, dbg_steps = 0, dbg_wait_acc = 0;
-      const long long dbg_t0 = clock64();
+      const long long dbg_t0 = SPMMDB_BSR_DBG(a) ? clock64() : 0;
       while (!done) {
-        const long long ta0 = (a.dbg & 32) ? clock64() : 0;
+        const long long ta0 = (SPMMDB_BSR_DBG(a) & 32) ? clock64() : 0;
         mbar_wait(&ctl->tmem_empty[acc], acc_phase[acc] ^ 1);
-        if (a.dbg & 32) dbg_wait_acc += clock64() - ta0;
+        if (SPMMDB_BSR_DBG(a) & 32) dbg_wait_acc += clock64() - ta0;
         tc_fence_after();
         uint32_t touched = 0;
         while (true) {
-          const long long tw0 = (a.dbg & 32) ? clock64() : 0;
+          const long long tw0 = (SPMMDB_BSR_DBG(a) & 32) ? clock64() : 0;
           mbar_wait(&ctl->full[stage], phase);
-          if (a.dbg & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
+          if (SPMMDB_BSR_DBG(a) & 32) { dbg_wait += clock64() - tw0; ++dbg_steps; }
           tc_fence_after();
           // broadcast from lane 0: tells the compiler the value (and the control flow below) is warp-uniform
           const uint32_t mask = __shfl_sync(0xffffffffu, ctl->meta[stage].mask, 0);
@@ -414,7 +424,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
           const uint32_t sB = smem_base + (uint32_t)stage * a.stage_bytes;
           const uint32_t sA16 = (sB + a.stage_b_bytes) >> 4;
           const uint32_t dcol = tmem_base + (uint32_t)(acc * acc_cols);
-          uint32_t m = (a.dbg & 4) ? 0u : mask;
+          uint32_t m = (SPMMDB_BSR_DBG(a) & 4) ? 0u : mask;
           while (m) {
             const int l0 = __ffs(m) - 1;
             const uint32_t tb = (touched >> l0) & 1u;
@@ -441,7 +451,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
           }
           touched |= mask;
           if (elect_one()) {
-            if (a.dbg & 8) mbar_arrive(&ctl->empty[stage]);
+            if (SPMMDB_BSR_DBG(a) & 8) mbar_arrive(&ctl->empty[stage]);
             else umma_commit(&ctl->empty[stage]);  // frees the stage when these MMAs have read it
           }
           __syncwarp();
@@ -450,7 +460,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
         acc_phase[acc] ^= 1;
         acc ^= 1;
       }
-      if ((a.dbg & 32) && blockIdx.x == 0 && lane == 0)
+      if ((SPMMDB_BSR_DBG(a) & 32) && blockIdx.x == 0 && lane == 0)
         printf("mma: total %lld cyc, steps %lld, wait(full) %lld cyc, wait(tmem_empty) %lld cyc\n", clock64() - dbg_t0,
                dbg_steps, dbg_wait, dbg_wait_acc);
     }
@@ -490,12 +500,35 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
             for (int j = 0; j < 32; ++j)
               if (!((tmask >> j) & 1u)) v[j] = 0u;
           }
-          if (!fok || (a.dbg & 16)) continue;
+          if (SPMMDB_BSR_DBG(a) & 16) continue;
           const int nrow = (int)min((int64_t)32, m_rows - row0);
+          if (!fok && a.c_layout == SPMMDB_ROW_MAJOR) continue;  // (the column-major path needs the whole warp)
           float* __restrict__ cp;
           int64_t cs;  // stride between consecutive rows of A in C
-          if (a.c_layout == SPMMDB_ROW_MAJOR) { cp = a.C + row0 * a.ldc + f; cs = a.ldc; }
-          else { cp = a.C + (int64_t)f * a.ldc + row0; cs = 1; }
+          if (a.c_layout != SPMMDB_ROW_MAJOR) {
+            // Column-major C (the reference's layout, rocsparse_bsrmm.h:102-108): a thread holds 32 consecutive rows of
+            // ONE feature, i.e. 128 contiguous bytes of C -- but the 32 lanes sit ldc floats apart.  Transpose the
+            // 32 x 32 tile through shared memory so that a warp store covers 32 consecutive rows of one feature
+            // (one full 128-byte line) instead of 32 lines 4 bytes at a time (C4: 5.0 -> see profiles/r2).
+            float* tb = tbuf_all + (warp & 3) * (32 * 33);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) tb[lane * 33 + j] = a.alpha * __uint_as_float(v[j]);
+            __syncwarp();
+            const int f0 = t * 128 + qd * 32;
+            const int nf = min(32, a.n - f0);
+            if (lane < nrow) {
+              float* __restrict__ cq = a.C + (int64_t)f0 * a.ldc + row0 + lane;
+              for (int ff = 0; ff < nf; ++ff, cq += a.ldc) {
+                float o = tb[ff * 33 + lane];
+                if (a.beta != 0.f) o = fmaf(a.beta, *cq, o);
+                *cq = o;
+              }
+            }
+            __syncwarp();
+            continue;
+          }
+          cp = a.C + row0 * a.ldc + f;
+          cs = a.ldc;
           if (nrow == 32 && a.beta == 0.f) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) cp[(int64_t)j * cs] = a.alpha * __uint_as_float(v[j]);
@@ -744,8 +777,11 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   a.tmem_cols = cps == 2 ? 256 : 512;
   a.NT = NT;
   a.G = NT / bs;
-  const int dbg_env = SPMMDB_TUNE("BSR_DEBUG_SKIP", 0);
-  a.dbg = dbg_env;
+#ifdef SPMMDB_BSR_DEBUG
+  a.dbg = SPMMDB_TUNE("BSR_DEBUG_SKIP", 0);
+#else
+  a.dbg = 0;
+#endif
   a.dir = dir; a.c_layout = c_layout;
   a.num_super = (mb + a.G - 1) / a.G;
   a.rowptr = rowptr; a.colind = colind; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
@@ -754,7 +790,8 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   const int cpt = 128 / fc;
   a.stage_b_bytes = (uint32_t)(tiles * cpt) * a.chunk_bytes;
   a.stage_bytes = (a.stage_b_bytes + (uint32_t)(NT * bs * esize) + 1023u) & ~1023u;
-  const size_t ctl_bytes = sizeof(TcSmemCtl) + 64;
+  // control block (+ the four 32 x 33 float transpose tiles of the column-major-C epilogue)
+  const size_t ctl_bytes = sizeof(TcSmemCtl) + 64 + (c_layout == SPMMDB_ROW_MAJOR ? 0 : 4 * 32 * 33 * sizeof(float) + 16);
   const size_t smem_max = cps == 2 ? 113 * 1024 : 227 * 1024;
   int stages = (int)((smem_max - 1024 - ctl_bytes) / a.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -796,7 +833,11 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   const int grid = a.num_super < nsm * cps ? a.num_super : nsm * cps;
   const int p_env = SPMMDB_TUNE("BSR_PRODUCERS", 0);
-  const int P = p_env >= 1 && p_env <= 3 ? p_env : 3;  // 4 producers with 3 stages did not finish in the r1l sweep: not offered
+  // A producer refills stage (its step) % stages and waits on that stage's `empty` parity: with more producers than
+  // stages two producers are a whole ring apart on the SAME barrier and the later one can pass a phase early (ABA) --
+  // the hang seen with 4 producers on 3 stages in r1l.  So P <= stages, always.
+  int P = p_env >= 1 && p_env <= 3 ? p_env : 3;
+  if (P > stages) P = stages;
   if (bf16) {
     if (P == 1) return launch_tc<true, 1>(a, mapB, mapA, grid, smem_bytes, st);
     if (P == 2) return launch_tc<true, 2>(a, mapB, mapA, grid, smem_bytes, st);

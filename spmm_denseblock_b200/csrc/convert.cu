@@ -721,6 +721,62 @@ extern "C" int spmmdb_divide_nnz(int m, int n, const int* rowptr, const int* col
   return SPMMDB_OK;
 }
 
+// Fill-decile histogram of the non-empty bs x bs blocks (calculate_block_density_dist, block_density_dist.cpp:47-86):
+// dist[d] = number of blocks whose fill lands in decile d, with the reference's own expression
+//   float occupy = (num * 1.0) / (bsize * bsize); int ith = (int)(occupy * 10); if (ith >= 10) ith = 9;
+// evaluated on the host to find, per decile, the smallest count that reaches it; the device then counts the blocks
+// with at least that many entries (the split's count pass) and the histogram is the difference of neighbours.
+extern "C" int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* colind, int block_dim,
+                                           int64_t* dist10_host, void* stream) {
+  if (m < 0 || n < 0 || block_dim <= 0 || block_dim > 128 || dist10_host == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  for (int d = 0; d < 10; ++d) dist10_host[d] = 0;
+  const int mb = (m + block_dim - 1) / block_dim;
+  if (mb == 0) return SPMMDB_OK;
+  if (rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int bnum = block_dim * block_dim;
+  auto decile = [&](int num) {
+    float occupy = (num * 1.0) / bnum;
+    int ith = (int)(occupy * 10);
+    return ith >= 10 ? 9 : ith;
+  };
+  int thr[10];
+  for (int d = 0; d < 10; ++d) {
+    thr[d] = INT_MAX;
+    for (int c = 1; c <= bnum; ++c)
+      if (decile(c) >= d) { thr[d] = c; break; }  // decile() is monotone in the count
+  }
+  const int ntiles = (m + kScanTile - 1) / kScanTile + 1;
+  int* ws = (int*)scratch(kScratchConvert, sizeof(int) * (2 * (size_t)mb + (size_t)m + ntiles + 16), st);
+  if (ws == nullptr) return SPMMDB_ERR_ALLOC;
+  int* bsr_counts = ws;
+  int* csr_counts = ws + mb;
+  int* sums = ws + mb + m;
+  int* tmp_rowptr = sums + ntiles + 4;  // mb + 1 entries
+  int64_t nnz = -1;
+  int rc = read_nnz(rowptr, m, st, &nnz);
+  if (rc != SPMMDB_OK) return rc;
+  int at_least[11] = {0};
+  for (int d = 0; d < 10; ++d) {
+    if (thr[d] == INT_MAX) { at_least[d] = 0; continue; }
+    if (d > 0 && thr[d] == thr[d - 1]) { at_least[d] = -1; continue; }  // same class as the decile below: filled in later
+    rc = use_br(m, n, block_dim, true, nnz, -1)
+             ? divide_br(false, SPMMDB_DIR_ROW, m, n, rowptr, colind, nullptr, block_dim, thr[d], bsr_counts, csr_counts,
+                         nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st)
+             : launch_divide<0>(SPMMDB_DIR_ROW, m, mb, block_dim, thr[d], rowptr, colind, nullptr, bsr_counts, csr_counts,
+                                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, st);
+    if (rc != SPMMDB_OK) return rc;
+    if ((rc = exclusive_scan(bsr_counts, mb, sums, tmp_rowptr, st)) != SPMMDB_OK) return rc;
+    SPMMDB_CUDA_OK(cudaMemcpyAsync(&at_least[d], tmp_rowptr + mb, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  }
+  for (int d = 1; d < 10; ++d)
+    if (at_least[d] < 0) at_least[d] = at_least[d - 1];
+  for (int d = 0; d < 10; ++d) dist10_host[d] = (int64_t)at_least[d] - at_least[d + 1];
+  return SPMMDB_OK;
+}
+
 extern "C" int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const int* colind, const float* val,
                                  int block_dim, float density, const int* bsr_rowptr, int* bsr_colind,
                                  float* bsr_val, const int* csr_rowptr, int* csr_colind, float* csr_val,

@@ -38,6 +38,7 @@ struct CsrArgs {
   int64_t ldb;          // in elements of B
   int b_bf16;           // stream kernel only: B holds bf16 (8 columns per 16-byte vector)
   const unsigned* hot;  // stream kernel only: bitmap of the columns whose B rows should stay in L2 (or null)
+  int hot_policy;       // L2 eviction class of the hot rows: 0 evict_last, 1 evict_normal
   int cold_policy;      // L2 eviction class of the other rows: 0 normal, 1 evict_first, 2 evict_unchanged
   float* C;
   int64_t ldc;
@@ -587,7 +588,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
   for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
   uint64_t pol_hot = 0, pol_cold = 0;
   if (HINT) {
-    pol_hot = policy_evict_last();
+    pol_hot = a.hot_policy == 1 ? policy_evict_normal() : policy_evict_last();
     pol_cold = a.cold_policy == 1 ? policy_evict_first() : (a.cold_policy == 2 ? policy_evict_unchanged() : policy_evict_normal());
   }
   // (column, value) chunk loads; with HINT the column's bit of the hot bitmap rides in the sign bit
@@ -828,6 +829,287 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
 }
 
 
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+
+// ---------------------------------------------------------------------------
+// Lean stream kernel: csrmm_stream_kernel's work distribution (items of `rpi` rows from a global counter, queued
+// long-row segments taken between items, partial sums added in segment order by the last finisher) and its
+// register gather, with the inner loop rebuilt around what ncu showed (profiles/r2c_*, r2d_*): the stream kernel
+// executes 44 (fp32) / 54 (bf16 B) warp instructions per non-zero for its 8 FMAs -- per-element range and row-end
+// tests with divergence scaffolding (BRA + BSSY + BSYNC = 9-11 per non-zero) -- and is issue-bound wherever DRAM
+// is not the limit (products-shaped graph with locality, bf16 B).  Here
+//   * batches are 8 non-zeros aligned to 8 ABSOLUTE indices, so a batch never straddles a 32-entry
+//     (column, value) chunk and its shuffles use constant lane offsets;
+//   * the row ends that fall inside a batch are ONE warp reduction (an 8-bit mask in a uniform register).  No
+//     row end (the common case): 8 x (value, FMAs) with no test at all.  Otherwise the batch is swept once per
+//     row piece with uniform branches around whole non-zeros, and the row store appears once in the code.
+// Each output element is still the sequential fp32 FMA chain in CSR order (bit-identical to csrmm_stream_kernel).
+// (A shared-memory ring fed by cp.async / cp.async.bulk instead of the register gather was built and measured in
+// r2b / r2d: correct, but LDGSTS costs 4 issue slots with its three padding instructions on this chip, UBLKCP ~10
+// per row through ELECT / R2UR, and the kernel is issue-bound: 5.0-6.4 ms where this one ... see profiles/.)
+template <int VEC, int MINB, bool BF16>
+__global__ void __launch_bounds__(256, MINB) csrmm_lean_kernel(const CsrArgs a) {
+  constexpr int G = 8;
+  using Ops = VecOps<float4>;
+  using BV = BVec<BF16>;
+  using Raw = typename BV::Raw;
+  constexpr int OV = BV::OV;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int nvec = a.K / (4 * OV);                 // 16-byte vectors per row of B
+  const Raw* __restrict__ Bv = reinterpret_cast<const Raw*>(a.B) + lane;
+  const uint32_t ldbv = (uint32_t)(a.ldb / (4 * OV));  // row pitch in 16-byte vectors (< 2^32: checked by the host)
+  const int nitems = (a.m + a.rpi - 1) / a.rpi;
+  const int kpadv = a.Kpad >> 2;
+  bool colok[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
+
+  int item = 0;
+  if (lane == 0) item = atomicAdd(a.counters + 3, 1);
+  item = __shfl_sync(FULL, item, 0);
+  int pending = a.inline_segs;
+  for (;;) {
+    // ---- pick work: a queued segment if there is one, else the item already claimed (as csrmm_stream_kernel)
+    int t = -1;
+    if (pending) {
+      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
+        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
+        else atomicAdd(a.counters + 5, 1);
+      }
+      t = __shfl_sync(FULL, t, 0);
+    }
+    pending = 0;
+    int next_item = item;
+    int nrows = 1, s = 0, e = 0, lng = 0;
+    float4* __restrict__ obase;
+    int ldo;
+    if (t >= 0) {
+      volatile unsigned long long* pe = a.seg_entry + t;
+      unsigned long long ent;
+      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
+      __threadfence();
+      pending = 1;
+      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));
+      if (lane == 0) {
+        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
+        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
+      }
+      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
+      ldo = 0;
+    } else {
+      if (item >= nitems) break;
+      if (lane == 0) {
+        next_item = atomicAdd(a.counters + 3, 1);
+        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
+      }
+      const int r0 = item * a.rpi;
+      nrows = min(a.rpi, a.m - r0);
+      if (lane < nrows) {
+        s = __ldg(a.rowptr + r0 + lane);
+        e = __ldg(a.rowptr + r0 + lane + 1);
+      }
+      lng = (e - s) > a.seg;
+      if (__any_sync(FULL, lng)) {
+        pending = a.inline_segs;
+        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
+      }
+      ldo = (int)(a.ldc >> 2);
+      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
+    }
+    const unsigned longmask = __ballot_sync(FULL, lng != 0);
+
+    // ---- runs of consecutive rows that are computed here (a queued long row ends a run)
+    int rb = 0;
+    while (rb < nrows) {
+      const unsigned lm = longmask >> rb;
+      const int re = lm ? rb + (__ffs(lm) - 1) : nrows;
+      if (re > rb) {
+        const int S = __shfl_sync(FULL, s, rb);
+        const int E = __shfl_sync(FULL, e, re - 1);
+        int cr = rb;
+        float4 acc[VEC][OV];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+#pragma unroll
+          for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
+        auto store_row = [&]() {  // row cr <- acc, acc <- 0
+          float4* __restrict__ Cv = obase + (int64_t)cr * ldo;
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) {
+            if (colok[i]) {
+#pragma unroll
+              for (int h = 0; h < OV; ++h) {
+                float4* o = Cv + OV * (lane + 32 * i) + h;
+                float4 out;
+                if (t >= 0) out = acc[i][h];
+                else if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+                else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+                else out = acc[i][h];
+                __stcs(o, out);
+              }
+            }
+#pragma unroll
+            for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
+          }
+          ++cr;
+        };
+        // rows that end at non-zero index `pos` with nothing in them: written as zeros (acc is zero here)
+        auto skip_empty = [&](int pos) {
+          while (cr < re && __shfl_sync(FULL, e, cr) == pos) store_row();
+        };
+        skip_empty(S);
+
+        // (column, value) chunks of 32: [p0, p0+32) holds the batch being gathered, the next one is the prefetch
+        int p0 = S & ~31;
+        int c0 = 0, c1 = 0;
+        float v0 = 0.f, v1 = 0.f;
+        {
+          const int i0 = p0 + lane, i1 = i0 + 32;
+          if (i0 >= S && i0 < E) { c0 = __ldg(a.colind + i0); v0 = __ldg(a.val + i0); }
+          if (i1 < E) { c1 = __ldg(a.colind + i1); v1 = __ldg(a.val + i1); }
+        }
+        const int k0 = S >> 3, k1 = (E + 7) >> 3;  // batches [k0, k1): batch k = non-zeros [8k, 8k + 8)
+        for (int k = k0; k < k1; ++k) {
+          const int q0 = k << 3;
+          if (q0 - p0 >= 32) {  // consumed a chunk: shift, fetch the one after the next
+            p0 += 32;
+            c0 = c1; v0 = v1;
+            const int i1 = p0 + 32 + lane;
+            c1 = 0; v1 = 0.f;
+            if (i1 < E) { c1 = __ldg(a.colind + i1); v1 = __ldg(a.val + i1); }
+          }
+          const int l0 = q0 & 31;  // the batch's first lane of the chunk registers
+          const int jlo = max(S - q0, 0), jhi = min(E - q0, G);
+          const bool whole = (jlo == 0) & (jhi == G);
+          // ---- gather: 8 B rows, VEC 16-byte vectors per lane each
+          Raw b[G][VEC];
+          float vv[G];
+          if (whole) {
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+              const unsigned cc = (unsigned)__shfl_sync(FULL, c0, l0 + j);
+              vv[j] = __shfl_sync(FULL, v0, l0 + j);
+              const Raw* __restrict__ brow = Bv + (uint64_t)cc * ldbv;
+#pragma unroll
+              for (int i = 0; i < VEC; ++i)
+                if (colok[i]) b[j][i] = ldg_raw(brow + 32 * i);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < G; ++j) {
+              const unsigned cc = (unsigned)__shfl_sync(FULL, c0, l0 + j);
+              vv[j] = __shfl_sync(FULL, v0, l0 + j);
+              if (j >= jlo && j < jhi) {
+                const Raw* __restrict__ brow = Bv + (uint64_t)cc * ldbv;
+#pragma unroll
+                for (int i = 0; i < VEC; ++i)
+                  if (colok[i]) b[j][i] = ldg_raw(brow + 32 * i);
+              }
+            }
+          }
+          // rows whose last non-zero lies in this batch: bit j = "a row ends after non-zero q0 + j"
+          const unsigned epos = (unsigned)(e - 1 - q0);
+          const unsigned endmask = __reduce_or_sync(FULL, (lane < nrows && epos < (unsigned)G) ? (1u << epos) : 0u);
+          if (whole && endmask == 0u) {
+            // whole batch inside one row (the common case): 8 x FMAs, no test
+#pragma unroll
+            for (int j = 0; j < G; ++j)
+#pragma unroll
+              for (int i = 0; i < VEC; ++i)
+                if (colok[i]) BV::fma(acc[i], vv[j], b[j][i]);
+          } else {
+            // one sweep per row piece [ja, jb): uniform branches around whole non-zeros, one copy of the row store
+            int ja = jlo;
+            while (ja < jhi) {
+              const unsigned em = endmask >> ja;
+              const bool ends = em != 0u && (ja + __ffs(em)) <= jhi;
+              const int jb = ends ? ja + __ffs(em) : jhi;
+#pragma unroll
+              for (int j = 0; j < G; ++j) {
+                if (j >= ja && j < jb) {
+#pragma unroll
+                  for (int i = 0; i < VEC; ++i)
+                    if (colok[i]) BV::fma(acc[i], vv[j], b[j][i]);
+                }
+              }
+              if (ends) {
+                store_row();
+                skip_empty(q0 + jb);
+              }
+              ja = jb;
+            }
+          }
+        }
+        while (cr < re) store_row();  // trailing rows (only reached when the run holds no non-zero at all)
+      }
+      rb = re + 1;
+    }
+
+    if (t >= 0) {
+      __threadfence();
+      __syncwarp();
+      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
+      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
+      int last = 0;
+      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
+      last = __shfl_sync(FULL, last, 0);
+      if (last) {
+        __threadfence();
+        if (lane == 0) a.done[seg_slot] = 0;
+        float4 acc[VEC][OV];
+        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
+        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i)
+            if (colok[i]) {
+#pragma unroll
+              for (int h = 0; h < OV; ++h) {
+                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
+                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
+              }
+            }
+        }
+        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+          if (colok[i]) {
+#pragma unroll
+            for (int h = 0; h < OV; ++h) {
+              float4* o = Cv + OV * (lane + 32 * i) + h;
+              float4 out;
+              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+              else out = acc[i][h];
+              __stcs(o, out);
+            }
+          }
+      }
+    } else {
+      item = __shfl_sync(FULL, next_item, 0);
+    }
+    pending = __shfl_sync(FULL, pending, 0);
+  }
+}
+
+template <int VEC, int MINB, bool BF16>
+int launch_lean(const CsrArgs& a, int nsm, cudaStream_t st) {
+  auto kernel = csrmm_lean_kernel<VEC, MINB, BF16>;
+  kernel<<<nsm * MINB, 256, 0, st>>>(a);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  kernel<<<nsm * MINB, 256, 0, st>>>(a);  // sweep: segments queued late
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
 // ---------------------------------------------------------------------------
 // Async stream kernel (K % 4 == 0, K <= 256): same work distribution and the same per-element FMA
 // chain as csrmm_stream_kernel, but the B-row gathers are cp.async (LDGSTS) copies into a per-warp
@@ -839,13 +1121,6 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
 // 2 CTAs x 8 warps x D*U rows x K*4 B = 192 KB are in flight per SM.
 // Rows longer than `seg` are queued for csrmm_long_kernel; the item is then processed as the runs
 // of short rows between them.
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
 template <int VEC, int U, int D, int MINB>
 __global__ void __launch_bounds__(256, MINB) csrmm_async_kernel(const CsrArgs a) {
   static_assert(D * U + U <= 32, "issue pointer must stay inside the two staged (col, val) chunks");
@@ -1123,6 +1398,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
   a.b_bf16 = b_bf16; a.hot = hot;
   a.cold_policy = SPMMDB_TUNE("CSR_COLD_POLICY", 1);
+  a.hot_policy = SPMMDB_TUNE("CSR_HOT_POLICY", 0);
   const int seg_override = current_segment_override();
   a.seg = seg_override ? seg_override : spmmdb_csrmm_segment_for(m, nnz);
   // Small matrices (C2: 1.1 M nnz, 64-entry segments) are latency-bound: a queued segment as a work unit costs
@@ -1181,6 +1457,11 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     a.rpi = rpi;
     const int vec = (K / 8 + 31) / 32;
     const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
+    const int bulk = SPMMDB_TUNE("CSR_LEAN", 0);
+    if (bulk) {
+      if (vec == 1) return bulk == 2 ? launch_lean<1, 4, true>(a, nsm, st) : launch_lean<1, 3, true>(a, nsm, st);
+      if (vec == 2) return launch_lean<2, 2, true>(a, nsm, st);
+    }  // wider rows: the stream kernel below (8 x 3 or 4 vectors per lane do not fit the register file)
     if (vec == 1) {
       if (variant == 1) return launch_stream<1, 8, 3, true>(a, nsm, long_ctas, st);
       if (variant == 2) return launch_stream<1, 16, 3, true>(a, nsm, long_ctas, st);
@@ -1203,6 +1484,11 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     if (rpi_env > 0) rpi = rpi_env < 32 ? rpi_env : 32;
     a.rpi = rpi;
     const int vec = (K / 4 + 31) / 32;
+    const int bulk = SPMMDB_TUNE("CSR_LEAN", 0);
+    if (bulk && a.inline_segs && a.hot == nullptr && vec <= 2) {
+      if (vec == 1) return bulk == 2 ? launch_lean<1, 4, false>(a, nsm, st) : launch_lean<1, 3, false>(a, nsm, st);
+      if (vec == 2) return launch_lean<2, 2, false>(a, nsm, st);
+    }
     const int async_env = SPMMDB_TUNE("CSR_ASYNC", 0);
     if (async_env && vec <= 2) {
       // ring per warp = D*U rows; 2 CTAs/SM x 8 warps x 12 KB = 192 KB in flight

@@ -137,10 +137,20 @@ int read_counted_file(const std::string& path, int** out, long long* count) {
   return SPMMDB_OK;
 }
 
-int check_csr(int n, long long nnz, const int* rowptr) {
+// Graph files are square adjacency matrices (n rows, n columns): a column id outside [0, n) would become an
+// out-of-bounds gather of a B row on the device, so it is refused here.
+int check_csr(int n, long long nnz, const int* rowptr, const int* colind) {
   if (n < 0 || rowptr[0] != 0 || rowptr[n] != nnz) return SPMMDB_ERR_INVALID_VALUE;
   for (int i = 0; i < n; ++i)
     if (rowptr[i + 1] < rowptr[i]) return SPMMDB_ERR_INVALID_VALUE;
+  const int parts = io_threads((size_t)nnz * 4);
+  std::vector<int> bad(parts, 0);
+  parallel_for(parts, [&](int i) {
+    for (long long j = nnz / parts * i, e = (i == parts - 1) ? nnz : nnz / parts * (i + 1); j < e; ++j)
+      if ((unsigned)colind[j] >= (unsigned)n) { bad[i] = 1; break; }
+  });
+  for (int b : bad)
+    if (b) return SPMMDB_ERR_INVALID_VALUE;
   return SPMMDB_OK;
 }
 
@@ -150,7 +160,7 @@ int read_text(const std::string& prefix, int* n, int64_t* nnz, int** rowptr, int
   int rc = read_counted_file(prefix + "_indptr.txt", &rp, &np1);
   if (rc == SPMMDB_OK) rc = read_counted_file(prefix + "_indices.txt", &ci, &nz);
   if (rc == SPMMDB_OK && np1 < 1) rc = SPMMDB_ERR_IO;
-  if (rc == SPMMDB_OK) rc = check_csr((int)np1 - 1, nz, rp);
+  if (rc == SPMMDB_OK) rc = check_csr((int)np1 - 1, nz, rp, ci);
   if (rc != SPMMDB_OK) { free(rp); free(ci); return rc; }
   *n = (int)np1 - 1; *nnz = nz; *rowptr = rp; *colind = ci;
   return SPMMDB_OK;
@@ -167,7 +177,7 @@ int read_edgelist(const std::string& path, int* n_out, int64_t* nnz_out, int** r
   if (!rp || !ci) { free(rp); free(ci); return SPMMDB_ERR_ALLOC; }
   for (long long e = 0; e < nnz; ++e) {
     long long x = v[2 + 2 * e], y = v[3 + 2 * e];
-    if (x < 0 || x >= n || y < -0x7fffffffLL || y > 0x7fffffffLL) { free(rp); free(ci); return SPMMDB_ERR_INVALID_VALUE; }
+    if (x < 0 || x >= n || y < 0 || y >= n) { free(rp); free(ci); return SPMMDB_ERR_INVALID_VALUE; }
     ++rp[x + 1];
   }
   for (long long i = 0; i < n; ++i) rp[i + 1] += rp[i];
@@ -212,7 +222,7 @@ int read_binary(const std::string& prefix, int* n, int64_t* nnz, int** rowptr, i
                           !read_fully(fd, ci, sizeof(int) * (size_t)h.nnz)))
     rc = SPMMDB_ERR_IO;
   close(fd);
-  if (rc == SPMMDB_OK) rc = check_csr((int)h.rows, h.nnz, rp);
+  if (rc == SPMMDB_OK) rc = check_csr((int)h.rows, h.nnz, rp, ci);
   if (rc != SPMMDB_OK) { free(rp); free(ci); return rc; }
   *n = (int)h.rows; *nnz = h.nnz; *rowptr = rp; *colind = ci;
   return SPMMDB_OK;

@@ -235,6 +235,16 @@ def heatmap(rowptr, colind, block_dim=256):
     return heat
 
 
+def block_fill_histogram(rowptr, colind, block_dim, n=None):
+    """calculate_block_density_dist (block_density_dist.cpp:47-86): blocks per fill decile, as a list of 10 ints."""
+    _dev(rowptr, colind)
+    m = rowptr.numel() - 1
+    dist = (C.c_int64 * 10)()
+    rc = lib().spmmdb_block_fill_histogram(m, m if n is None else n, _p(rowptr), _p(colind), block_dim, dist, _stream())
+    check(rc, "spmmdb_block_fill_histogram")
+    return list(dist)
+
+
 def block_metrics(rowptr, colind, block_dim):
     """analyzeBlockSparseMetrics (reorder_graph.cc:12-24): (nnzb, density, utilization, average)."""
     n, nnz = rowptr.numel() - 1, colind.numel()

@@ -193,3 +193,16 @@ def test_divide_cli_and_agreement(tmp_path):
     for tb in (0, 1):
         ref = sums[("cusparse", "fp32", tb)]
         assert abs(sums[("rocsparse", "fp32", tb)] - ref) <= 1e-3 * max(1.0, abs(ref))
+
+
+@pytest.mark.gpu
+def test_known_answer_programs(tmp_path):
+    """csrmm / bsrmm without arguments (csrmm.cu:26-218, bsrmm.cu:35-177): the reference's example matrices, its
+    printed format, goldens G1 / G2 of SURVEY 8c."""
+    _build()
+    rc, out = _run([os.path.join(BIN, "csrmm")], str(tmp_path))
+    assert rc == 0 and "testing examples" in out and out.rstrip().endswith("end"), out
+    assert "190.000000 80.000000 510.000000 520.000000 430.000000 240.000000 1230.000000 1200.000000" in out
+    rc, out = _run([os.path.join(BIN, "bsrmm")], str(tmp_path))
+    assert rc == 0, out
+    assert out.count("61.000000 26.000000 63.000000 43.000000 139.000000 92.000000 153.000000 97.000000") == 2, out

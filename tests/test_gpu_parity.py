@@ -653,3 +653,16 @@ def test_permute_full_size_products_property(pkg):
     assert bool(((nci[1:] > nci[:-1]) | ~same_row).all())
     brp, bci, _ = pkg.permute_csr(nrp, nci, None, inv)
     assert torch.equal(brp, rp) and torch.equal(bci, ci)
+
+
+@pytest.mark.parametrize("bs", [2, 3, 4, 8, 16, 32, 64])
+def test_block_fill_histogram_divide_metrics_bit_exact(pkg, oracle, bs):
+    """spmmdb_block_fill_histogram == calculate_block_density_dist (block_density_dist.cpp:47-86), every decile,
+    on a matrix with sparse background and dense diagonal bands (so the upper deciles are populated)."""
+    rng = np.random.default_rng(bs)
+    n = 1000
+    rp, ci = _banded_graph(rng, n, band=max(bs, 4), p_dense=0.85, avg=7)
+    want = oracle.block_density_dist(rp, ci, bs)
+    got = pkg.block_fill_histogram(dev(rp), dev(ci), bs)
+    assert got == want.tolist(), (got, want.tolist())
+    assert sum(got) == pkg.block_metrics(dev(rp), dev(ci), bs)[0]

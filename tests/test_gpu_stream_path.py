@@ -39,16 +39,27 @@ def err_vs(oracle, got, ref64, rp, ci, v, Bm, K, alpha=1.0, beta=0.0, C0=None):
     return float(np.max(np.abs(got.astype(np.float64) - ref64) / np.maximum(scale, 1e-30)))
 
 
-@pytest.fixture
-def forced_stream(pkg):
-    """Small matrices through the benchmark's kernel: no small-matrix path, segments of 256 taken inline."""
+@pytest.fixture(params=["registers", "bulk1", "bulk2"])
+def forced_stream(pkg, request):
+    """Small matrices through the benchmark's kernels: no small-matrix path, segments of 256 taken inline.
+    `registers` = csrmm_stream_kernel, `bulk1` / `bulk2` = csrmm_lean_kernel at two occupancies (the same gather with
+    the inner loop rebuilt around 8-aligned batches and a row-end mask)."""
     pkg.set_tuning("CSR_SMALL", 0)
     pkg.set_tuning("CSR_INLINE", 1)
+    pkg.set_tuning("CSR_LEAN", {"registers": 0, "bulk1": 1, "bulk2": 2}[request.param])
     pkg.set_csrmm_segment(256)
     yield 256
     pkg.set_csrmm_segment(0)
     pkg.set_tuning("CSR_SMALL", None)
     pkg.set_tuning("CSR_INLINE", None)
+    pkg.set_tuning("CSR_LEAN", None)
+
+
+@pytest.fixture(params=[0, 1, 2])
+def bulk_mode(pkg, request):
+    pkg.set_tuning("CSR_LEAN", request.param)
+    yield request.param
+    pkg.set_tuning("CSR_LEAN", None)
 
 
 def hub_matrix(seed, m=6000, k=9000, avg=8):
@@ -186,7 +197,9 @@ def _config_case(name, scale, K, seed=1234, **over):
     ("c5_products", 0.1, 128, {}),                   # VEC 1
     ("c3_proteins", 0.25, 128, {}),                  # rows kernel (271 nnz per row)
 ])
-def test_csrmm_config_shapes_vs_oracle(pkg, oracle, name, scale, K, over):
+def test_csrmm_config_shapes_vs_oracle(pkg, oracle, bulk_mode, name, scale, K, over):
+    if bulk_mode and name != "c5_products":
+        pytest.skip("the lean kernel serves the stream kernel's shapes with inline segments (nnz >= 4 M)")
     rp, ci, val, B, n = _config_case(name, scale, K, **over)
     C = torch.full((n, K), float("nan"), device="cuda")
     pkg.csrmm(rp, ci, val, B, C, n, n, K)
@@ -234,7 +247,7 @@ def _bf16_round(x):
 
 @pytest.mark.parametrize("K", [64, 128, 256, 512, 1024])
 @pytest.mark.parametrize("alpha,beta", [(1.0, 0.0), (0.5, -2.0)])
-def test_csrmm_ex_bf16_b(pkg, oracle, K, alpha, beta):
+def test_csrmm_ex_bf16_b(pkg, oracle, bulk_mode, K, alpha, beta):
     """B stored as bf16, fp32 accumulate: exactly the fp32 kernel's arithmetic on the rounded B (bit for bit on
     rows of one segment), and within the stated 1e-2 of the product with the unrounded B."""
     rng, (rp, ci, v) = hub_matrix(400 + K, m=3000, k=5000)

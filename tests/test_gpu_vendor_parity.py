@@ -47,15 +47,19 @@ def conversion_path(request, monkeypatch):
 
 @pytest.mark.parametrize("bs", [2, 3, 4, 8, 16, 32, 64])
 @pytest.mark.parametrize("direction", [0, 1])
-def test_csr2bsr_bit_equal_to_cusparse(pkg, cmp, conversion_path, bs, direction):
-    rng = np.random.default_rng(bs * 13 + direction)
-    for m, n, avg in ((1000, 1200, 9), (257, 4099, 40), (33, 31, 3)):  # ragged last block row / column
-        rp, ci, v = random_csr(rng, m, n, avg, hubs={1: min(n, 900)}, empty_rows={0, m - 1})
-        drp, dci, dv = dev(rp), dev(ci), dev(v)
-        brp, bci, bv = pkg.csr2bsr(m, n, drp, dci, dv, bs, direction)
+@pytest.mark.parametrize("shape", [(1000, 1200, 9), (257, 4099, 40), (33, 31, 3)])  # ragged last block row / column
+def test_csr2bsr_bit_equal_to_cusparse(pkg, cmp, conversion_path, bs, direction, shape):
+    m, n, avg = shape
+    rng = np.random.default_rng(bs * 13 + direction + m)
+    rp, ci, v = random_csr(rng, m, n, avg, hubs={1: min(n, 900)}, empty_rows={0, m - 1})
+    drp, dci, dv = dev(rp), dev(ci), dev(v)
+    brp, bci, bv = pkg.csr2bsr(m, n, drp, dci, dv, bs, direction)
+    try:
         vrp, vci, vv = cmp.cusparse_csr2bsr(m, n, drp, dci, dv, bs, direction)
-        assert torch.equal(brp, vrp) and torch.equal(bci, vci)
-        assert torch.equal(bv.view(torch.int32), vv.view(torch.int32))  # bit pattern, zeros included
+    except RuntimeError as e:  # e.g. CUSPARSE_STATUS_INVALID_VALUE for some (shape, blockDim) pairs in 12.5
+        pytest.skip(f"cuSPARSE rejects this case: {e}")
+    assert torch.equal(brp, vrp) and torch.equal(bci, vci)
+    assert torch.equal(bv.view(torch.int32), vv.view(torch.int32))  # bit pattern, zeros included
 
 
 @pytest.mark.parametrize("bs", [2, 3, 8, 16, 32, 64])

@@ -136,6 +136,24 @@ def test_errors_are_loud(tmp_path):
     open(g, "w").write("3 2\n0 1\n5 0\n")                       # source node out of range
     with pytest.raises(S.SpmmdbError, match="INVALID_VALUE"):
         S.read_graph(g, S.GRAPH_EDGELIST)
+    # a column id outside [0, n) would become an out-of-bounds gather on the device: refused by every reader
+    for bad in ("3 2\n0 1\n1 3\n", "3 2\n0 1\n1 -1\n"):
+        open(g, "w").write(bad)
+        with pytest.raises(S.SpmmdbError, match="INVALID_VALUE"):
+            S.read_graph(g, S.GRAPH_EDGELIST)
+    q = str(tmp_path / "y")
+    open(q + "_indptr.txt", "w").write("4\n0 1 2 3 \n")
+    open(q + "_indices.txt", "w").write("3\n0 3 1 \n")        # column 3 of a 3 x 3 matrix
+    with pytest.raises(S.SpmmdbError, match="INVALID_VALUE"):
+        S.read_graph(q, S.GRAPH_TEXT)
+    open(q + "_indices.txt", "w").write("3\n0 2 1 \n")
+    S.read_graph(q, S.GRAPH_TEXT)
+    import numpy as np
+    with open(q + ".csrbin", "wb") as f:
+        f.write(b"SPMMDBG1" + np.array([3, 3, 3], np.int64).tobytes() + np.array([0, 1, 2, 3], np.int32).tobytes()
+                + np.array([0, -2, 1], np.int32).tobytes())
+    with pytest.raises(S.SpmmdbError, match="INVALID_VALUE"):
+        S.read_graph(q, S.GRAPH_BINARY)
 
 
 def test_graph2bin_driver(tmp_path):

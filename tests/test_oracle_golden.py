@@ -180,3 +180,16 @@ def test_divide_threshold_matches_reference_expression():
             thr = pkg.divide_threshold(bs, dens)
             ok = lambda c: np.float32((c * 1.0) / (bs * bs)) >= np.float32(dens)  # noqa: E731
             assert ok(thr) and thr >= 1 and (thr == 1 or not ok(thr - 1)), (bs, dens, thr)
+
+
+def test_block_density_dist_restatement_matches_the_reference(oracle):
+    """calculate_block_density_dist (block_density_dist.cpp:47-86): the numpy restatement against the reference's
+    own function compiled from /root/reference (oracle/_ref/libref_host.so) on seeded inputs."""
+    if oracle.ref_host_lib() is None or not hasattr(oracle.ref_host_lib(), "ref_block_density_dist"):
+        pytest.skip("oracle/_ref/libref_host.so not built")
+    from helpers import random_csr
+    rng = np.random.default_rng(5)
+    for n, avg in ((600, 30), (257, 90), (64, 50)):
+        rp, ci, _ = random_csr(rng, n, n, avg)
+        for bs in (2, 3, 4, 8, 16, 32):
+            assert np.array_equal(oracle.block_density_dist(rp, ci, bs), oracle.ref_block_density_dist(rp, ci, bs))

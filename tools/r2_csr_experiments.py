@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--iters", type=int, default=8)
     ap.add_argument("--quick", action="store_true")
     ap.add_argument("--only", default="")
+    ap.add_argument("--policies", type=int, default=1, help="0: no L2-policy cases, 1: the short list, 2: the r2a sweep")
     a = ap.parse_args()
     import torch
 
@@ -85,11 +86,31 @@ def main():
             return med
 
         run("fp32 drop-in", lambda: pkg.csrmm(rp, ci, val, B, Cref, n, n, K), alg)
-        for variant in ((2, 3) if not a.quick else ()):
+        for bulk in (1, 2):
+            pkg.set_tuning("CSR_LEAN", bulk)
+            for rpi in (8, 16, 32):
+                pkg.set_tuning("CSR_RPI", rpi)
+                Cm.fill_(float("nan"))
+                run(f"fp32 bulk {bulk} rpi {rpi}", lambda: pkg.csrmm(rp, ci, val, B, Cm, n, n, K), alg,
+                    bit_equal=None)
+                emit(**base, case=f"fp32 bulk {bulk} rpi {rpi} bits equal to the register kernel",
+                     value=bool(torch.equal(Cm, Cref)))
+            pkg.set_tuning("CSR_RPI", None)
+            pkg.set_tuning("CSR_LEAN", None)
+        if a.policies:
+            hot, n_hot = pkg.csr_hot_columns(n, ci, 64 * (1 << 20) // (K * 4))
+            pkg.set_tuning("CSR_HOT_POLICY", 1)
+            for pol in (1, 0, 2):
+                pkg.set_tuning("CSR_COLD_POLICY", pol)
+                run(f"fp32 hot(evict_normal hint) 64 MB cold_policy {pol}",
+                    lambda: pkg.csrmm_ex(rp, ci, val, B, Cm, n, n, K, hot=hot), alg, n_hot=n_hot)
+            pkg.set_tuning("CSR_COLD_POLICY", None)
+            pkg.set_tuning("CSR_HOT_POLICY", None)
+        for variant in ((2, 3) if not a.quick and a.policies else ()):
             pkg.set_tuning("CSR_VARIANT", variant)
             run(f"fp32 variant {variant}", lambda: pkg.csrmm(rp, ci, val, B, Cm, n, n, K), alg)
             pkg.set_tuning("CSR_VARIANT", None)
-        for budget_mb in (48, 64, 80, 96) if not a.quick else (64,):
+        for budget_mb in ((48, 64, 80, 96) if not a.quick else (64,)) if a.policies == 2 else ():
             rows = budget_mb * (1 << 20) // (K * 4)
             hot, n_hot = pkg.csr_hot_columns(n, ci, rows)
             for pol in (1, 0, 2) if not a.quick else (1,):
@@ -99,7 +120,7 @@ def main():
                 pkg.set_tuning("CSR_COLD_POLICY", None)
             assert torch.equal(Cm, Cref)
         # with an L2 set-aside for persisting (evict_last) lines
-        if max_persist.value > 0 and not a.quick:
+        if max_persist.value > 0 and not a.quick and a.policies == 2:
             for frac in (0.5, 0.75):
                 sz = int(max_persist.value * frac)
                 rt.cudaDeviceSetLimit(6, C.c_size_t(sz))  # cudaLimitPersistingL2CacheSize
@@ -118,7 +139,19 @@ def main():
             pkg.set_tuning("CSR_VARIANT", None)
         err = float((Cm - Cref).abs().max() / Cref.abs().max())
         emit(**base, case="bf16 B max |diff| / max |C| vs fp32", value=err)
-        for variant in (0, 1) if not a.quick else (0,):
+        Cb = Cm.clone()
+        for bulk in (1, 2):
+            pkg.set_tuning("CSR_LEAN", bulk)
+            for rpi in (8, 16, 32):
+                pkg.set_tuning("CSR_RPI", rpi)
+                Cm.fill_(float("nan"))
+                run(f"bf16 B bulk {bulk} rpi {rpi}", lambda: pkg.csrmm_ex(rp, ci, val, Bb, Cm, n, n, K), alg_b)
+                emit(**base, case=f"bf16 B bulk {bulk} rpi {rpi} bits equal to the register kernel",
+                     value=bool(torch.equal(Cm, Cb)))
+            pkg.set_tuning("CSR_RPI", None)
+            pkg.set_tuning("CSR_LEAN", None)
+        del Cb
+        for variant in ((0, 1) if not a.quick else (0,)) if a.policies == 2 else ():
             pkg.set_tuning("CSR_VARIANT", variant)
             for budget_mb in (48, 64, 80, 96) if not a.quick else (64,):
                 rows = budget_mb * (1 << 20) // (K * 2)
