@@ -305,7 +305,8 @@ def main():
             small = nnzs < (4 << 20)
             kernel_name = ("csrmm_rows_pipe_kernel + long-row kernels (small-matrix path)" if small and 32 < K <= 256 else
                            "csrmm_rows_kernel" if nnzs // max(ms_, 1) >= 64 else
-                           "csrmm_stream_kernel (queued long-row segments taken between items)")
+                           "csrmm_lean_kernel (8-aligned gather batches, queued long-row segments taken between items)"
+                           if K <= 256 else "csrmm_stream_kernel (queued long-row segments taken between items)")
             launches_per_step = 5 if small and 32 < K <= 256 else 2
         else:
             t0 = time.perf_counter()
@@ -320,7 +321,7 @@ def main():
             alg_bytes = 4 * (ms_ + 1) + 8 * nnzs + 2 * n * K + 4 * ms_ * K
             gather = 2 * nnzs * K
             dtype = "f32 accumulate, bf16-stored B"
-            kernel_name = "csrmm stream / bulk kernel (bf16 B)"
+            kernel_name = "csrmm_lean_kernel (bf16-stored B)" if K <= 512 else "csrmm_stream_kernel (bf16-stored B)"
         flops = 2.0 * nnz * K
         out_rows = Cs
         roof_extra = {"gather_bytes_per_launch": gather,

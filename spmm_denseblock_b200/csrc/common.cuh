@@ -27,7 +27,7 @@ void set_last_error(const char* what, cudaError_t err, const char* file, int lin
 // share a buffer; calls on different streams (or devices) never share one, so they
 // may be in flight together.  At most kMaxScratchStreams streams per device hold
 // scratch at a time: the least recently used one is synchronised and released.
-enum ScratchSlot { kScratchCsrLong = 0, kScratchCsrPartial, kScratchCsrDone, kScratchCsrEntry, kScratchLayoutB, kScratchLayoutC,
+enum ScratchSlot { kScratchCsrLong = 0, kScratchCsrPartial, kScratchCsrDone, kScratchCsrEntry, kScratchCsrEpoch, kScratchLayoutB, kScratchLayoutC,
                    kScratchConvert, kScratchBsr, kScratchBsrA, kScratchBsrB, kScratchHostA, kScratchHostB, kScratchHostC,
                    kScratchSlots };
 void* scratch(int slot, size_t bytes, cudaStream_t stream);

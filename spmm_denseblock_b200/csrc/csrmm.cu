@@ -45,6 +45,7 @@ struct CsrArgs {
   float alpha, beta;
   int seg;              // row segment length (power of two)
   // long-row queue (scratch)
+  int* epoch_dev;       // device word holding the call number (see csrmm_begin_kernel)
   int* counters;        // [0] = long rows, [1] = segments, [2] = overflow flag, [3] = work items taken,
                         // [4] = segments taken (stream path)
   LongRow* long_rows;   // capacity cap_rows
@@ -54,11 +55,26 @@ struct CsrArgs {
   float* partial;       // capacity cap_segs * Kpad floats
   int cap_rows, cap_segs;
   int Kpad;             // K rounded up to 4
-  int epoch;            // call counter: tells this call's queue entries from stale ones
+  int epoch;            // call counter: tells this call's queue entries from stale ones.  Filled in ON THE DEVICE from
+                        // counters[7] (csrmm_begin_kernel increments it once per call), not by the host
   int rpi;              // stream kernel: rows per work item (<= 32)
   int inline_segs;      // stream kernel: warps take queued segments between items (else: long-row kernel after)
   int prequeued;        // the long-row queue was built by csrmm_scan_long_kernel: row kernels only skip long rows
 };
+
+// First launch of every call: clears the queue counters and advances the call number (a scratch word of its own that
+// is never re-allocated while the other queue buffers live, so numbers never repeat against their stale entries).  The
+// number is device state so that a call captured into a CUDA graph gets a fresh one on every replay (stale queue
+// entries of the previous replay must not look current).
+__global__ void csrmm_begin_kernel(int* counters, int* epoch_dev) {
+  const int l = threadIdx.x;
+  if (l < 8) counters[l] = 0;
+  if (l == 8) {
+    int e = *epoch_dev + 1;
+    if (e <= 0) e = 1;
+    *epoch_dev = e;
+  }
+}
 
 template <typename V> struct VecOps;
 template <> struct VecOps<float4> {
@@ -177,7 +193,9 @@ __device__ __forceinline__ void store_row(const Args& a, int row, int sub, int v
 // Main kernel: one group (LPR lanes) per row.  K > 32 lanes * VEC vectors is
 // covered by looping over column tiles inside the kernel.
 template <typename V, int LPR, int VEC, int U>
-__global__ void __launch_bounds__(256) csrmm_rows_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256) csrmm_rows_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   constexpr int GPW = 32 / LPR;
   using Ops = VecOps<V>;
   const int lane = threadIdx.x & 31;
@@ -232,7 +250,9 @@ __global__ void __launch_bounds__(256) csrmm_rows_kernel(const CsrArgs a) {
 // row, so the rowptr -> colind -> B chain of a row overlaps the gathers of the row before it.  Same
 // arithmetic per row as csrmm_rows_kernel (bit-identical output), same long-row queue.
 template <typename V, int LPR, int VEC, int U>
-__global__ void __launch_bounds__(256, 3) csrmm_rows_pipe_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256, 3) csrmm_rows_pipe_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   constexpr int GPW = 32 / LPR;
   using Ops = VecOps<V>;
   const int lane = threadIdx.x & 31;
@@ -332,7 +352,9 @@ __device__ __forceinline__ bool queue_long_row(const CsrArgs& a, int row, int le
 // nnz was too small) is computed here by the whole warp, one float4 / float column per lane, as the sequential
 // chain over the whole row -- what the rows kernels do with such a row.
 template <typename V>
-__global__ void __launch_bounds__(256) csrmm_scan_long_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256) csrmm_scan_long_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   using Ops = VecOps<V>;
   constexpr unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -366,7 +388,9 @@ __global__ void __launch_bounds__(256) csrmm_scan_long_kernel(const CsrArgs a) {
 // One vector column per lane, RB partial rows in flight per lane: a hub row with hundreds of segments was the
 // critical path when the last warp to finish a segment did this inside the long-row kernel.
 template <typename V>
-__global__ void __launch_bounds__(256) csrmm_reduce_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256) csrmm_reduce_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   using Ops = VecOps<V>;
   constexpr int RB = 16;
   const int lane = threadIdx.x & 31;
@@ -406,7 +430,9 @@ __global__ void __launch_bounds__(256) csrmm_reduce_kernel(const CsrArgs a) {
 // Long-row kernel: one group per queued segment (all column tiles), partial
 // sums to scratch; csrmm_reduce_kernel adds them afterwards.
 template <typename V, int LPR, int VEC, int U>
-__global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256) csrmm_long_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   constexpr int GPW = 32 / LPR;
   using Ops = VecOps<V>;
   const int lane = threadIdx.x & 31;
@@ -571,7 +597,9 @@ __device__ __forceinline__ uint64_t policy_evict_unchanged() {
 }
 
 template <int VEC, int U, int MINB, bool BF16, bool HINT>
-__global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   using Ops = VecOps<float4>;
   using BV = BVec<BF16>;
   using Raw = typename BV::Raw;
@@ -852,9 +880,11 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // Each output element is still the sequential fp32 FMA chain in CSR order (bit-identical to csrmm_stream_kernel).
 // (A shared-memory ring fed by cp.async / cp.async.bulk instead of the register gather was built and measured in
 // r2b / r2d: correct, but LDGSTS costs 4 issue slots with its three padding instructions on this chip, UBLKCP ~10
-// per row through ELECT / R2UR, and the kernel is issue-bound: 5.0-6.4 ms where this one ... see profiles/.)
+// per row through ELECT / R2UR, and the kernel is issue-bound: 5.0-6.4 ms where this one takes 3.1-4.6 ms: profiles/r2b, r2d, r2e.)
 template <int VEC, int MINB, bool BF16>
-__global__ void __launch_bounds__(256, MINB) csrmm_lean_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256, MINB) csrmm_lean_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   constexpr int G = 8;
   using Ops = VecOps<float4>;
   using BV = BVec<BF16>;
@@ -1122,7 +1152,9 @@ int launch_lean(const CsrArgs& a, int nsm, cudaStream_t st) {
 // Rows longer than `seg` are queued for csrmm_long_kernel; the item is then processed as the runs
 // of short rows between them.
 template <int VEC, int U, int D, int MINB>
-__global__ void __launch_bounds__(256, MINB) csrmm_async_kernel(const CsrArgs a) {
+__global__ void __launch_bounds__(256, MINB) csrmm_async_kernel(const CsrArgs a_in) {
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
   static_assert(D * U + U <= 32, "issue pointer must stay inside the two staged (col, val) chunks");
   using Ops = VecOps<float4>;
   constexpr unsigned FULL = 0xffffffffu;
@@ -1408,7 +1440,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   if (b_bf16) a.inline_segs = 1;  // the separate long-row kernel reads fp32 B only
   a.prequeued = 0;
   a.Kpad = (K + 3) & ~3;
-  a.epoch = next_epoch();
+  a.epoch = 0;  // set on the device
   // worst case: every segment queued.  segments <= nnz/seg + long rows, long rows <= nnz/seg
   const int64_t max_long = nnz / a.seg + 1;
   const int64_t max_segs = 2 * max_long;
@@ -1425,14 +1457,17 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   int* done = (int*)scratch(kScratchCsrDone, sizeof(int) * (size_t)max_long, st);
   unsigned long long* entry =
       (unsigned long long*)scratch(kScratchCsrEntry, sizeof(unsigned long long) * (size_t)max_segs, st);
-  if (q == nullptr || part == nullptr || done == nullptr || entry == nullptr) return SPMMDB_ERR_ALLOC;
+  a.epoch_dev = (int*)scratch(kScratchCsrEpoch, 64, st);  // fixed size: allocated once per (device, stream)
+  if (q == nullptr || part == nullptr || done == nullptr || entry == nullptr || a.epoch_dev == nullptr)
+    return SPMMDB_ERR_ALLOC;
   a.counters = (int*)q;
   a.long_rows = (LongRow*)(q + hdr);
   a.seg_owner = (int*)(q + hdr + sizeof(LongRow) * max_long);
   a.done = done;
   a.seg_entry = entry;
   a.partial = part;
-  SPMMDB_CUDA_OK(cudaMemsetAsync(a.counters, 0, 32, st));
+  csrmm_begin_kernel<<<1, 32, 0, st>>>(a.counters, a.epoch_dev);  // zero the queue counters, next call number
+  SPMMDB_CUDA_OK(cudaGetLastError());
   const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
   const int lc_env = SPMMDB_TUNE("CSR_LONG_CTAS", 0);
   const int long_ctas = nsm * (lc_env > 0 ? lc_env : 4);  // C2 sweep: 2 / 4 / 8 -> 0.166 / 0.160 / 0.156 ms
@@ -1457,7 +1492,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     a.rpi = rpi;
     const int vec = (K / 8 + 31) / 32;
     const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
-    const int bulk = SPMMDB_TUNE("CSR_LEAN", 0);
+    const int bulk = SPMMDB_TUNE("CSR_LEAN", 1);  // 0: csrmm_stream_kernel, 1 / 2: csrmm_lean_kernel (two occupancies)
     if (bulk) {
       if (vec == 1) return bulk == 2 ? launch_lean<1, 4, true>(a, nsm, st) : launch_lean<1, 3, true>(a, nsm, st);
       if (vec == 2) return launch_lean<2, 2, true>(a, nsm, st);
@@ -1484,7 +1519,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     if (rpi_env > 0) rpi = rpi_env < 32 ? rpi_env : 32;
     a.rpi = rpi;
     const int vec = (K / 4 + 31) / 32;
-    const int bulk = SPMMDB_TUNE("CSR_LEAN", 0);
+    const int bulk = SPMMDB_TUNE("CSR_LEAN", 1);  // 0: csrmm_stream_kernel, 1 / 2: csrmm_lean_kernel (two occupancies)
     if (bulk && a.inline_segs && a.hot == nullptr && vec <= 2) {
       if (vec == 1) return bulk == 2 ? launch_lean<1, 4, false>(a, nsm, st) : launch_lean<1, 3, false>(a, nsm, st);
       if (vec == 2) return launch_lean<2, 2, false>(a, nsm, st);

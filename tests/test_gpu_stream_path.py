@@ -55,7 +55,7 @@ def forced_stream(pkg, request):
     pkg.set_tuning("CSR_LEAN", None)
 
 
-@pytest.fixture(params=[0, 1, 2])
+@pytest.fixture(params=[0, 1, 2])  # 0: csrmm_stream_kernel, 1 / 2: csrmm_lean_kernel (the default is 1)
 def bulk_mode(pkg, request):
     pkg.set_tuning("CSR_LEAN", request.param)
     yield request.param
@@ -308,3 +308,42 @@ def test_csrmm_ex_hot_columns_same_bits(pkg, oracle, forced_stream, K, bf16):
     if not bf16:
         ref = oracle.csrmm(rp, ci, v, B, K)
         assert err_vs(oracle, plain.cpu().numpy(), ref, rp, ci, v, B, K) <= TOL_FP32
+
+
+# ----------------------------------------------------------------------------- CUDA graph capture
+@pytest.mark.parametrize("path", ["small_matrix", "stream_inline", "lean_inline"])
+def test_csrmm_call_replays_correctly_from_a_cuda_graph(pkg, oracle, path):
+    """A call (after one warm-up call on the capture stream, so that no scratch is allocated during capture; nnz
+    passed, so that nothing synchronises) can be captured into a CUDA graph -- including the small-matrix path's side stream -- and every
+    replay gets a fresh call number on the device: stale queue entries of the previous replay never look current."""
+    if path != "small_matrix":
+        pkg.set_tuning("CSR_SMALL", 0)
+        pkg.set_tuning("CSR_INLINE", 1)
+        pkg.set_tuning("CSR_LEAN", 1 if path == "lean_inline" else 0)
+        pkg.set_csrmm_segment(256)
+    try:
+        K = 128
+        rng, (rp, ci, v) = hub_matrix(77)
+        m, k = rp.size - 1, 9000
+        d = [dev(x) for x in (rp, ci, v)]
+        Bs = [rng.uniform(-1, 1, (k, K)).astype(np.float32) for _ in range(3)]
+        B = dev(Bs[0])
+        C = torch.empty(m, K, device="cuda")
+        cap = torch.cuda.Stream()
+        with torch.cuda.stream(cap):  # warm-up ON THE CAPTURE STREAM: library scratch is per (device, stream)
+            pkg.csrmm(*d, B, C, m, k, K, nnz=ci.size)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=cap):
+            pkg.csrmm(*d, B, C, m, k, K, nnz=ci.size)
+        for it in (1, 2, 0, 1):
+            B.copy_(dev(Bs[it]))
+            C.fill_(float("nan"))
+            g.replay()
+            torch.cuda.synchronize()
+            ref = oracle.csrmm(rp, ci, v, Bs[it], K)
+            assert err_vs(oracle, C.cpu().numpy(), ref, rp, ci, v, Bs[it], K) <= TOL_FP32, (path, it)
+    finally:
+        pkg.set_csrmm_segment(0)
+        for knob in ("CSR_SMALL", "CSR_INLINE", "CSR_LEAN"):
+            pkg.set_tuning(knob, None)
