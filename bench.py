@@ -476,6 +476,9 @@ def main():
             extra[f"allgather_plus_spmm_ms_slabs{slabs}"] = timed(
                 lambda: mg.sharded_csrmm(rps, cis, vals, Bown, ranges, Cf, n, K, slabs=slabs))
         extra["sharded_entry_matches_replicated"] = bool(torch.equal(Cf, Cs))
+        extra["allgather_path"] = {0: "NCCL send / recv group", 1: "CUDA IPC peer pushes by copy engines + NCCL barriers",
+                                   2: "pack kernel storing into every rank's replica over NVLink (CUDA IPC) + NCCL "
+                                      "barriers"}[pkg.get_tuning("MG_PEER", 2)]
         best = min(extra[f"allgather_plus_spmm_ms_slabs{s_}"] for s_ in (1, 2, 4))
         extra["value_with_allgather"] = flops / (best * 1e-3) / 1e9
         extra["allgather_inbound_gbs"] = 4.0 * (n - ms_) * K / (extra["allgather_B_ms"] * 1e-3) / 1e9
