@@ -510,7 +510,7 @@ def main():
             def e2e_step():
                 for k_ in d:
                     d[k_].copy_(h[k_], non_blocking=True)
-                mg.sharded_csrmm(d["rp"], d["ci"], d["val"], d["B"], ranges, Cs, n, K, slabs=4)
+                mg.sharded_csrmm(d["rp"], d["ci"], d["val"], d["B"], ranges, Cs, n, K, slabs=2)
                 hC.copy_(Cs, non_blocking=True)
                 stream.synchronize()
         else:

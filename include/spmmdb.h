@@ -285,7 +285,7 @@ int spmmdb_shard_plan(const int* h_rowptr, int m, int parts, int align, int* bou
  *                            group of send / recv pairs (every rank sends to every peer at once)
  *   spmmdb_sharded_csrmm_f32  C_local = alpha * A_local * B + beta * C_local where every rank passes ITS rows of
  *                            B (B_local, [rows][ldb]) and its shard of A (rowptr rebased to 0, global column
- *                            ids).  K is cut into `slabs` feature slabs (0 = default 4); slab s + 1 is gathered
+ *                            ids).  K is cut into `slabs` feature slabs (0 = default 2); slab s + 1 is gathered
  *                            on a communication stream while the SpMM of slab s runs on `stream`.  The replica of
  *                            B lives in library memory (k * K floats per rank, slab-major).  Same bits as the
  *                            single-GPU call on the whole matrix when every rank has set the whole matrix's segment length

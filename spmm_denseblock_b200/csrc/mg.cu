@@ -319,7 +319,7 @@ extern "C" int spmmdb_sharded_csrmm_f32(spmmdb_mg* g, int k, int K, int64_t nnz_
     return SPMMDB_ERR_INVALID_VALUE;
   if (K % 4 != 0 || ldb % 4 != 0 || ((uintptr_t)B_local % 16) != 0) return SPMMDB_ERR_NOT_SUPPORTED;
   cudaStream_t st = (cudaStream_t)stream;
-  if (slabs <= 0) slabs = SPMMDB_TUNE("MG_SLABS", 4);
+  if (slabs <= 0) slabs = SPMMDB_TUNE("MG_SLABS", 2);
   if (slabs > 16) slabs = 16;
   while (slabs > 1 && (K % slabs != 0 || (K / slabs) % 32 != 0)) --slabs;  // a slab keeps whole 128-byte lines
   const int Ks = K / slabs;

@@ -63,7 +63,7 @@ def main():
             with torch.cuda.stream(cap):  # library scratch is per (device, stream): warm up on the capture stream
                 call()
             torch.cuda.synchronize()
-            ok = bool(torch.allclose(C, Cref, rtol=1e-5, atol=1e-5))
+            ok = bool(torch.allclose(C, Cref, rtol=1e-4, atol=1e-4))
             gr = torch.cuda.CUDAGraph()
             with torch.cuda.graph(gr, stream=cap):
                 call()
