@@ -283,7 +283,7 @@ def main():
     bs = int("".join(ch for ch in a.op if ch.isdigit()) or 0) if not a.op.startswith("csr") else 0
     math = MATH[a.math]
     launches_per_step = 2
-    cci = None
+    hyb = None
     if a.op in ("csr", "csr_bf16b"):
         ranges = shard.shard_plan(rp, world)  # C ABI: spmmdb_shard_plan
         lo, hi = ranges[rank]
@@ -334,16 +334,18 @@ def main():
         Bp[:n] = B
         Cs = torch.zeros(mp, K, device=dev)
         t0 = time.perf_counter()
+        hyb = None
         if a.op.startswith("hybrid"):
-            crp, cci, cv, brp, bci, bv = pkg.divide(n, n, rp, ci, val, bs, a.density)
+            hyb = pkg.Hybrid(n, n, rp, ci, val, bs, a.density)  # spmmdb_hybrid_create: the split, kept on the device
+            nnzb, rem = hyb.nnzb, hyb.csr_nnz
         else:
             brp, bci, bv = pkg.csr2bsr(n, n, rp, ci, val, bs)
+            nnzb, rem = bci.numel(), 0
         torch.cuda.synchronize()
         extra["conversion_ms_once"] = (time.perf_counter() - t0) * 1e3
-        nnzb = bci.numel()
-        in_blocks = nnz - (cci.numel() if cci is not None else 0)
+        in_blocks = nnz - rem
         graph_info.update(block_size=bs, nnzb=nnzb, fill=in_blocks / max(nnzb * bs * bs, 1),
-                          nnz_in_blocks=in_blocks, remainder_nnz=(cci.numel() if cci is not None else 0))
+                          nnz_in_blocks=in_blocks, remainder_nnz=rem)
         if a.op.startswith("block_gemm"):
             bvc = bv.view(nnzb, bs, bs).transpose(1, 2).contiguous().view(-1)  # column-major blocks (block_cublas.cu)
             Zc = torch.zeros(K, mp, device=dev)
@@ -357,16 +359,14 @@ def main():
             kernel_name = "bsrmm_tc_kernel (grouped block GEMM)" if math else "bsrmm_simt_kernel"
             launches_per_step = 4
         elif a.op.startswith("hybrid"):
+            Cs = torch.zeros(n, K, device=dev)
+
             def step():
-                # divide.cu:348-373: C = A_csr * B, then C += A_bsr * B
-                rc = L.spmmdb_csrmm_f32(n, n, K, cci.numel(), crp.data_ptr(), cci.data_ptr(), cv.data_ptr(),
-                                        Bp.data_ptr(), K, 0, Cs.data_ptr(), K, 0, 1.0, 0.0, sp)
-                assert rc == 0, rc
-                rc = L.spmmdb_bsrmm_f32(0, 1, mb, K, mb, nnzb, bs, 1.0, bv.data_ptr(), brp.data_ptr(), bci.data_ptr(),
-                                        Bp.data_ptr(), K, 1.0, Cs.data_ptr(), K, 0, math, sp)
-                assert rc == 0, rc
+                # divide.cu:348-373 behind one call: C = A_csr * B, then C += A_bsr * B (spmmdb_hybrid_spmm_f32);
+                # B and C keep their n rows, no padding to whole blocks
+                hyb.spmm(B, Cs, K, math=math)
             out_rows = Cs
-            kernel_name = "csrmm (remainder) + bsrmm_tc_kernel (dense blocks)"
+            kernel_name = "csrmm (remainder) + bsrmm_tc_kernel (dense blocks) through spmmdb_hybrid_spmm_f32"
             launches_per_step = 6
         else:
             def step():
@@ -379,8 +379,8 @@ def main():
         flops = 2.0 * nnz * K
         dense_flops = 2.0 * nnzb * bs * bs * K
         alg_bytes = 4 * (mb + 1) + 4 * nnzb + 4 * nnzb * bs * bs + 4 * mp * K + 4 * mp * K
-        if cci is not None:
-            alg_bytes += 4 * (n + 1) + 8 * cci.numel()
+        if hyb is not None:
+            alg_bytes += 4 * (n + 1) + 8 * rem
         dtype = {0: "f32", 1: "tf32 inputs, f32 accumulate", 2: "bf16 inputs, f32 accumulate"}[math]
         roof_extra = {"dense_flops_per_launch": dense_flops}
         ms_, nnzs, lo, hi = n, nnz, 0, n
@@ -507,20 +507,26 @@ def main():
                    "all-gather-v of B overlapped with the SpMM per feature slab), D2H of this rank's C rows")
             h2d = 4 * (ms_ + 1) + 8 * nnzs + 4 * ms_ * K
 
+            marks = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
             def e2e_step():
+                marks[0].record()
                 for k_ in d:
                     d[k_].copy_(h[k_], non_blocking=True)
+                marks[1].record()
                 mg.sharded_csrmm(d["rp"], d["ci"], d["val"], d["B"], ranges, Cs, n, K, slabs=2)
+                marks[2].record()
                 hC.copy_(Cs, non_blocking=True)
+                marks[3].record()
                 stream.synchronize()
         else:
             # the op's device inputs from pinned host copies, the device call(s) through the C ABI, C back to the host
             if a.op == "csr_bf16b":
                 names = dict(rp=rps, ci=cis, val=vals, B=Bb)
+            elif hyb is not None:
+                names = dict(B=B)  # the split operator stays on the device (made once per graph); B is the step's input
             else:
                 names = dict(brp=brp, bci=bci, B=Bp, bv=(bvc if a.op.startswith("block_gemm") else bv))
-                if cci is not None:
-                    names.update(crp=crp, cci=cci, cv=cv)
             h = {k_: v_.cpu().pin_memory() for k_, v_ in names.items()}
             api = f"pinned host copies of the {a.op} operands -> H2D -> C-ABI device call(s) -> D2H of C"
             h2d = sum(v_.numel() * v_.element_size() for v_ in h.values())
@@ -543,6 +549,14 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_ms = float(tt.item())
         e2e_ok = abs(float(hC.double().sum().item()) - checksum) <= 1e-6 * max(1.0, abs(checksum))
+        if world > 1:
+            # where the step goes on this rank (device timeline of the last step; the ranks share the host's memory and
+            # PCIe switches, which is why the copies run far below one GPU's PCIe rate)
+            extra["e2e_breakdown_ms_rank0"] = {"h2d_A_shard_and_B_rows": marks[0].elapsed_time(marks[1]),
+                                               "allgather_plus_spmm": marks[1].elapsed_time(marks[2]),
+                                               "d2h_C_rows": marks[2].elapsed_time(marks[3]),
+                                               "h2d_GBps": h2d / marks[0].elapsed_time(marks[1]) / 1e6,
+                                               "d2h_GBps": hC.numel() * 4 / marks[2].elapsed_time(marks[3]) / 1e6}
         e2e = {"value": flops / (e2e_ms * 1e-3) / 1e9, "unit": "GFLOP/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": hC.numel() * 4, "ms_per_step": e2e_ms, "matches_device_path": bool(e2e_ok),
                "api": api}

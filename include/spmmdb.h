@@ -217,6 +217,24 @@ int spmmdb_divide_f32(int dir, int m, int n, const int* rowptr, const int* colin
                       int block_dim, float density, const int* bsr_rowptr, int* bsr_colind, float* bsr_val,
                       const int* csr_rowptr, int* csr_colind, float* csr_val, void* stream);
 
+/* The hybrid product as one object -- the BSR entry to use on graph adjacency matrices (at the 1-3 % block fill a
+ * reordering leaves, plain BSR multiplies mostly zeros; the split sends the dense blocks to the tensor cores and the
+ * rest to the CSR kernel).  What the reference's `divide` program does around divide_matrix (divide.cu:205-391):
+ *   spmmdb_hybrid_create     splits A (device CSR, val NULL = unit weights) once and keeps both parts in device memory
+ *                            owned by the handle; synchronises `stream`
+ *   spmmdb_hybrid_spmm_f32   C = alpha * A * B + beta * C as  C = alpha * A_csr * B + beta * C;  C += alpha * A_bsr * B
+ *                            (divide.cu:348-373).  Row-major B [n][ldb] and C [m][ldc]; m and n need NOT be multiples of
+ *                            block_dim and neither B nor C is padded (the reference drivers pad both).  math: SPMMDB_MATH_*
+ *                            of the block part.
+ *   spmmdb_hybrid_info       number of dense blocks and of remainder entries */
+typedef struct spmmdb_hybrid spmmdb_hybrid;
+int spmmdb_hybrid_create(int m, int n, const int* rowptr, const int* colind, const float* val, int block_dim,
+                         float density, spmmdb_hybrid** out, void* stream);
+int spmmdb_hybrid_info(const spmmdb_hybrid* h, int64_t* nnzb, int64_t* csr_nnz);
+int spmmdb_hybrid_spmm_f32(const spmmdb_hybrid* h, int K, const float* B, int64_t ldb, float* C, int64_t ldc,
+                           float alpha, float beta, int math, void* stream);
+int spmmdb_hybrid_destroy(spmmdb_hybrid* h);
+
 /* --------------------------------------------------------------------------
  * Apply a node permutation on the device (the reordering algorithms themselves stay on
  * the CPU and only produce old2new; one new id per old id, a bijection of 0..n-1).

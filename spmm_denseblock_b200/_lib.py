@@ -39,6 +39,10 @@ SIGNATURES = {
     "spmmdb_divide_nnz": [C.c_int, C.c_int, vp, vp, C.c_int, C.c_float, vp, vp, C.POINTER(C.c_int),
                           C.POINTER(C.c_int), vp],
     "spmmdb_divide_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_float, vp, vp, vp, vp, vp, vp, vp],
+    "spmmdb_hybrid_create": [C.c_int, C.c_int, vp, vp, vp, C.c_int, C.c_float, C.POINTER(vp), vp],
+    "spmmdb_hybrid_info": [vp, C.POINTER(c_i64), C.POINTER(c_i64)],
+    "spmmdb_hybrid_spmm_f32": [vp, C.c_int, vp, c_i64, vp, c_i64, C.c_float, C.c_float, C.c_int, vp],
+    "spmmdb_hybrid_destroy": [vp],
     "spmmdb_permute_csr_f32": [C.c_int, vp, vp, vp, vp, vp, vp, vp, vp],
     "spmmdb_permute_rows_f32": [C.c_int, C.c_int, vp, c_i64, vp, vp, c_i64, vp],
     "spmmdb_block_fill_histogram": [C.c_int, C.c_int, vp, vp, C.c_int, C.POINTER(c_i64), vp],

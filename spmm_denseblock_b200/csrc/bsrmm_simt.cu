@@ -26,6 +26,7 @@ struct BsrArgs {
   float* C;
   int64_t ldc;
   int c_layout;
+  int64_t b_rows, c_rows;  // rows of B that exist / rows of C that may be written (RowClip)
 };
 
 template <int BS, int TN>
@@ -69,7 +70,8 @@ __global__ void __launch_bounds__(TN) bsrmm_simt_kernel(const BsrArgs a) {
         for (int j = 0; j < BS; ++j) {
           if (j < cols) {
             const int64_t brow = col0 + j0 + j;
-            const float b = a.trans_b ? __ldg(a.B + brow * a.ldb + c) : __ldg(a.B + (int64_t)c * a.ldb + brow);
+            const float b = brow >= a.b_rows ? 0.f
+                            : (a.trans_b ? __ldg(a.B + brow * a.ldb + c) : __ldg(a.B + (int64_t)c * a.ldb + brow));
             if (BS % 4 == 0) {
               const float4* __restrict__ a4 = reinterpret_cast<const float4*>(As + j * BS);
 #pragma unroll
@@ -94,7 +96,7 @@ __global__ void __launch_bounds__(TN) bsrmm_simt_kernel(const BsrArgs a) {
   const int64_t row0 = (int64_t)ib * bs + r0;
 #pragma unroll
   for (int r = 0; r < BS; ++r) {
-    if (r < rows) {
+    if (r < rows && row0 + r < a.c_rows) {
       float* dst = (a.c_layout == SPMMDB_COL_MAJOR) ? a.C + (int64_t)c * a.ldc + row0 + r
                                                     : a.C + (row0 + r) * a.ldc + c;
       // same epilogue arithmetic as rocsparse_bsrmm_impl.h:382-388
@@ -117,7 +119,8 @@ int launch(const BsrArgs& a, cudaStream_t st) {
 int bsrmm_simt(int dir, int trans_b, int mb, int n, int bs, float alpha, const float* val, const int* rowptr,
                const int* colind, const float* B, int64_t ldb, float beta, float* C, int64_t ldc, int c_layout,
                cudaStream_t st) {
-  BsrArgs a{dir, trans_b, mb, n, bs, alpha, beta, val, rowptr, colind, B, ldb, C, ldc, c_layout};
+  const RowClip clip = current_row_clip();
+  BsrArgs a{dir, trans_b, mb, n, bs, alpha, beta, val, rowptr, colind, B, ldb, C, ldc, c_layout, clip.b_rows, clip.c_rows};
   if (bs <= 4) return launch<4>(a, st);
   if (bs <= 8) return launch<8>(a, st);
   if (bs <= 16) return launch<16>(a, st);

@@ -154,6 +154,7 @@ struct TcArgs {
   int mb, n, bs, G, NT, tiles, nchunks, stages;
   int dir, c_layout;
   int num_super;
+  int64_t m_valid;        // rows of C that may be written (mb * bs unless a RowClip is set)
   int tmem_cols;          // 512 (one CTA per SM) or 256 (two CTAs per SM)
   int dbg;                // developer timing experiments: 1 = no A loads, 2 = no B loads, 4 = no MMAs
   int b_one;              // B slab fetched by one 3-D TMA box (n is a multiple of the chunk width)
@@ -469,7 +470,7 @@ bsrmm_tc_kernel(const TcArgs a, const __grid_constant__ CUtensorMap mapB, const 
     const int qd = warp & 3;  // TMEM lane quarter this warp may access
     int acc = 0;
     uint32_t full_phase[2] = {0, 0};
-    const int64_t m_rows = (int64_t)a.mb * a.bs;
+    const int64_t m_rows = a.m_valid;
     const int cpb = 32 / a.bs;  // block rows per 32 accumulator columns (0 when bs = 64)
     while (true) {
       mbar_wait(&ctl->tmem_full[acc], full_phase[acc]);
@@ -723,7 +724,9 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
     // a block row wider than the 128-byte swizzle span (tf32, bs = 64) is not laid out by one TMA box
     return SPMMDB_ERR_NOT_SUPPORTED;
   }
-  const int64_t krows = (int64_t)kb * bs;
+  const RowClip clip = current_row_clip();
+  // rows of B the TMA maps cover: boxes that reach past them are zero-filled by the hardware
+  const int64_t krows = (int64_t)kb * bs < clip.b_rows ? (int64_t)kb * bs : clip.b_rows;
   const int fc = 128 / esize;
   const int tiles = (n + 127) / 128;
   const int nchunks = (n + fc - 1) / fc;
@@ -792,6 +795,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
 #endif
   a.dir = dir; a.c_layout = c_layout;
   a.num_super = (mb + a.G - 1) / a.G;
+  a.m_valid = (int64_t)mb * bs < clip.c_rows ? (int64_t)mb * bs : clip.c_rows;
   a.rowptr = rowptr; a.colind = colind; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
   a.chunk_bytes = (uint32_t)bs * 128u;
   a.block_bytes = (uint32_t)(bs * bs * esize);

@@ -1,5 +1,6 @@
 // common.cu -- error capture, device queries, tuning knobs and grow-only scratch for libspmmdb.
 #include <limits.h>
+#include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -148,6 +149,11 @@ int tune_lookup(TuneSlot& slot, const char* name, int dflt) {
   __atomic_store_n(&slot.packed, ((unsigned long long)gen << 32) | (unsigned)v, __ATOMIC_RELEASE);
   return v;
 }
+
+namespace { thread_local RowClip tl_clip = {INT64_MAX, INT64_MAX}; }
+RowClip current_row_clip() { return tl_clip; }
+ScopedRowClip::ScopedRowClip(int64_t b_rows, int64_t c_rows) : before_(tl_clip) { tl_clip = RowClip{b_rows, c_rows}; }
+ScopedRowClip::~ScopedRowClip() { tl_clip = before_; }
 
 int next_epoch() {
   int e = g_epoch.fetch_add(1, std::memory_order_relaxed) + 1;

@@ -48,6 +48,17 @@ struct ScopedSegment {  // pins the segment length for the calls this thread mak
   int before_;
 };
 
+// Row limits for the BSR kernels, set by library entry points whose matrix size is not a multiple of the block size
+// (spmmdb_hybrid_spmm_f32): rows of B at or beyond b_rows read as zero, rows of C at or beyond c_rows are not written.
+// The reference's contract (B and C padded to whole blocks, run_bsrmm.cu:86-94) is the default: no limit.
+struct RowClip { int64_t b_rows, c_rows; };
+RowClip current_row_clip();
+struct ScopedRowClip {
+  ScopedRowClip(int64_t b_rows, int64_t c_rows);
+  ~ScopedRowClip();
+  RowClip before_;
+};
+
 int next_epoch();      // process-wide call counter (atomic), never 0
 
 int device_sm();       // compute capability major*10+minor of the current device, cached

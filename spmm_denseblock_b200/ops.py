@@ -202,6 +202,39 @@ def divide(m, n, rowptr, colind, val, block_dim, density, direction=DIR_ROW):
     return csr_rowptr, csr_colind, csr_val, bsr_rowptr, bsr_colind, bsr_val
 
 
+class Hybrid:
+    """spmmdb_hybrid: A split once into dense blocks (tensor-core BSR) + remainder (CSR); spmm() multiplies both
+    parts into one C.  The recommended BSR entry for (re-ordered) graph adjacency matrices."""
+
+    def __init__(self, m, n, rowptr, colind, val, block_dim, density):
+        _dev(rowptr, colind, val)
+        self._h = C.c_void_p(0)
+        rc = lib().spmmdb_hybrid_create(m, n, _p(rowptr), _p(colind), _p(val), block_dim, density, C.byref(self._h),
+                                        _stream())
+        check(rc, "spmmdb_hybrid_create")
+        a, b = C.c_int64(0), C.c_int64(0)
+        lib().spmmdb_hybrid_info(self._h, C.byref(a), C.byref(b))
+        self.m, self.n, self.block_dim, self.nnzb, self.csr_nnz = m, n, block_dim, a.value, b.value
+
+    def spmm(self, B, C_out, K, ldb=None, ldc=None, alpha=1.0, beta=0.0, math=MATH_TF32):
+        _dev(B, C_out)
+        rc = lib().spmmdb_hybrid_spmm_f32(self._h, K, _p(B), K if ldb is None else ldb, _p(C_out),
+                                          K if ldc is None else ldc, alpha, beta, math, _stream())
+        check(rc, "spmmdb_hybrid_spmm_f32")
+        return C_out
+
+    def close(self):
+        if self._h:
+            lib().spmmdb_hybrid_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def permute_csr(rowptr, colind, val, old2new):
     """A' = P A P^T (permutate, reorder_strategy.cc:26-39) on the device.  Returns (rowptr, colind, val)."""
     _dev(rowptr, colind, val, old2new)

@@ -666,3 +666,31 @@ def test_block_fill_histogram_divide_metrics_bit_exact(pkg, oracle, bs):
     got = pkg.block_fill_histogram(dev(rp), dev(ci), bs)
     assert got == want.tolist(), (got, want.tolist())
     assert sum(got) == pkg.block_metrics(dev(rp), dev(ci), bs)[0]
+
+
+@pytest.mark.parametrize("n,bs", [(1000, 16), (1000, 32), (1024, 32), (777, 16)])
+@pytest.mark.parametrize("math,tol", [(0, TOL_FP32), (1, TOL_TC), (2, TOL_TC)])
+def test_hybrid_divide_object_ragged_sizes(pkg, oracle, n, bs, math, tol):
+    """spmmdb_hybrid_*: the split kept as one object, C = alpha * A * B + beta * C through CSR (remainder) + BSR
+    (dense blocks), with m, n NOT multiples of the block size and neither B nor C padded (the BSR kernels clip).
+    Guard rows after C catch a write past row m."""
+    rng = np.random.default_rng(n + bs + math)
+    K = 128
+    rp, ci = _banded_graph(rng, n, band=bs, p_dense=0.8, avg=6)
+    v = rng.uniform(-1, 1, ci.size).astype(np.float32)
+    B = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    h = pkg.Hybrid(n, n, dev(rp), dev(ci), dev(v), bs, 0.3)
+    assert h.nnzb > 0 and 0 < h.csr_nnz < ci.size
+    buf = torch.full((n + 64, K), 7.0, device="cuda")
+    buf[:n] = dev(C0)
+    Bbuf = torch.full((n + 64, K), float("nan"), device="cuda")  # rows past n must never be read into the result
+    Bbuf[:n] = dev(B)
+    h.spmm(Bbuf[:n], buf[:n], K, alpha=0.5, beta=-1.5, math=math)
+    torch.cuda.synchronize()
+    assert torch.all(buf[n:] == 7.0)
+    ref = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=0.5, beta=-1.5)
+    scale = 0.5 * oracle.csrmm(rp, ci, np.abs(v), np.abs(B), K) + 1.5 * np.abs(C0)
+    err = float(np.max(np.abs(buf[:n].cpu().numpy().astype(np.float64) - ref) / np.maximum(scale, 1e-30)))
+    assert err <= tol, err
+    h.close()
