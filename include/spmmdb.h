@@ -140,7 +140,7 @@ int spmmdb_get_csrmm_segment(void);     /* the override, 0 = automatic */
  *   C        column-major (ldc >= mb*bs) like the reference, or row-major
  *            [mb*bs][ldc] with c_layout = SPMMDB_ROW_MAJOR (extension)
  *   math     SPMMDB_MATH_FP32 (CUDA cores), _TF32 or _BF16 (tcgen05 tensor
- *            cores, block_dim in {8,16,32,64}; other shapes run the fp32 kernel)
+ *            cores: block_dim 16 or 32, and 64 with bf16; every other shape runs the fp32 kernel)
  * Returns the mathematical product -- the reference kernel's output-column
  * bug (rocsparse_bsrmm_impl.h:27,326,413) is not reproduced.
  * ------------------------------------------------------------------------ */
