@@ -691,6 +691,21 @@ int launch_tc(const TcArgs& a, const CUtensorMap& mapB, const CUtensorMap& mapA,
 
 }  // namespace
 
+// Tensor map of a row-major matrix whose box is ONE whole row (cols elements, no swizzle): what the CSR TMA-gather
+// kernel's tile::gather4 copies address, four rows per instruction (csrmm.cu).
+bool make_map_rows(CUtensorMap* map, bool bf16, const void* base, uint64_t cols, uint64_t rows, uint64_t row_bytes) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr || cols == 0 || cols > 256 || ((uintptr_t)base % 16) != 0 || row_bytes % 16 != 0) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)cols, 1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
 // Shapes the tensor-core kernel takes; everything else runs the fp32 CUDA-core kernel.
 bool bsrmm_tc_supported(int trans_b, int n, int bs, int64_t ldb, const float* B, const float* val, int c_layout,
                         int64_t ldc, const float* C) {

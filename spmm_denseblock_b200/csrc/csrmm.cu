@@ -22,9 +22,12 @@
 #include <mutex>
 #include <utility>
 
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace spmmdb {
+bool make_map_rows(CUtensorMap* map, bool bf16, const void* base, uint64_t cols, uint64_t rows, uint64_t row_bytes);  // bsrmm_tc.cu
 namespace {
 
 struct LongRow { int row; int seg_base; int nseg; int epoch; };
@@ -36,6 +39,7 @@ struct CsrArgs {
   const float* val;
   const float* B;       // fp32 rows, or (b_bf16) bf16 rows behind the same pointer
   int64_t ldb;          // in elements of B
+  int b_rows;           // rows of B (the TMA-gather kernel's tensor map needs the extent)
   int b_bf16;           // stream kernel only: B holds bf16 (8 columns per 16-byte vector)
   const unsigned* hot;  // stream kernel only: bitmap of the columns whose B rows should stay in L2 (or null)
   int hot_policy;       // L2 eviction class of the hot rows: 0 evict_last, 1 evict_normal
@@ -1151,6 +1155,332 @@ int launch_lean(const CsrArgs& a, int nsm, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------
+// TMA-gather kernel: the lean kernel's work distribution and multiply loop, with the B-row gather handed to the
+// tensor memory accelerator.  Blackwell's tile::gather4 mode of cp.async.bulk.tensor copies FOUR rows of a 2-D
+// tensor, named by four independent row coordinates, into consecutive shared-memory rows with one instruction:
+// exactly a CSR gather with the column indices as coordinates.  Per warp a ring of NS stages x 8 rows (two gather4
+// per stage, issued by one lane, completing on the stage's mbarrier); all lanes read the rows back as conflict-free
+// 16-byte shared loads.  ~3 issue slots per non-zero for the gather instead of the register kernel's LDG + address
+// arithmetic, nothing held in registers while in flight (NS * 8 rows per warp x 12 warps = 192 KB per SM), and the
+// multiply phase never waits on a long scoreboard.  Same sequential FMA chain per output element (bit-identical,
+// tested).  MEASURED (profiles/r2n): C5 spec'd fp32 6.89 ms vs 6.98 for the lean kernel (both DRAM-bound), but C5
+// local fp32 5.1 vs 4.15 ms and bf16 B 3.7-4.4 vs 3.1-4.3 ms: the TMA unit feeds an SM no faster than its LDG path
+// (the L2 -> SM port is the ceiling either way) and 12 warps multiply slower than 16-24.  Opt-in (CSR_TMA = 1 / 2).
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_gather4(uint32_t dst, const CUtensorMap* map, int col, int r0, int r1, int r2, int r3,
+                                            uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+      ::"r"(dst), "l"(map), "r"(col), "r"(r0), "r"(r1), "r"(r2), "r"(r3), "r"(bar) : "memory");
+}
+
+template <int VEC, int NS, int WARPS, bool BF16>
+__global__ void __launch_bounds__(WARPS * 32, 1) csrmm_tma_kernel(const CsrArgs a_in, const __grid_constant__ CUtensorMap mapB) {
+  static_assert(NS == 2 || NS == 4, "the issue pointer must stay within two (column, value) chunks of the consume pointer");
+  CsrArgs a = a_in;
+  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
+  constexpr int G = 8;
+  using Ops = VecOps<float4>;
+  using BV = BVec<BF16>;
+  using Raw = typename BV::Raw;
+  constexpr int OV = BV::OV;
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(128) unsigned char tma_smem[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nvec = a.K / (4 * OV);                 // 16-byte vectors per row of B
+  const uint32_t rowb = (uint32_t)nvec * 16u;      // bytes per gathered row = the tensor map's box
+  // per warp: a ring of NS stages x 8 rows, then NS mbarriers (one per stage)
+  const uint32_t warp_bytes = (uint32_t)(NS * G) * rowb + 128u;
+  unsigned char* my = tma_smem + (size_t)wid * warp_bytes;
+  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(my);
+  const uint32_t bars_s = ring_s + (uint32_t)(NS * G) * rowb;
+  const Raw* ring = reinterpret_cast<const Raw*>(my) + lane;
+  if (lane < NS) mbar_init(bars_s + 8u * lane, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncwarp();
+  unsigned gk = 0;  // stages this warp has issued and consumed so far: stage s of the ring is in its (gk / NS)-th use
+  const int nitems = (a.m + a.rpi - 1) / a.rpi;
+  const int kpadv = a.Kpad >> 2;
+  bool colok[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
+
+  int item = 0;
+  if (lane == 0) item = atomicAdd(a.counters + 3, 1);
+  item = __shfl_sync(FULL, item, 0);
+  int pending = a.inline_segs;
+  for (;;) {
+    // ---- pick work: a queued segment if there is one, else the item already claimed (as csrmm_stream_kernel)
+    int t = -1;
+    if (pending) {
+      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
+        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
+        else atomicAdd(a.counters + 5, 1);
+      }
+      t = __shfl_sync(FULL, t, 0);
+    }
+    pending = 0;
+    int next_item = item;
+    int nrows = 1, s = 0, e = 0, lng = 0;
+    float4* __restrict__ obase;
+    int ldo;
+    if (t >= 0) {
+      volatile unsigned long long* pe = a.seg_entry + t;
+      unsigned long long ent;
+      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
+      __threadfence();
+      pending = 1;
+      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));
+      if (lane == 0) {
+        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
+        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
+      }
+      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
+      ldo = 0;
+    } else {
+      if (item >= nitems) break;
+      if (lane == 0) {
+        next_item = atomicAdd(a.counters + 3, 1);
+        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
+      }
+      const int r0 = item * a.rpi;
+      nrows = min(a.rpi, a.m - r0);
+      if (lane < nrows) {
+        s = __ldg(a.rowptr + r0 + lane);
+        e = __ldg(a.rowptr + r0 + lane + 1);
+      }
+      lng = (e - s) > a.seg;
+      if (__any_sync(FULL, lng)) {
+        pending = a.inline_segs;
+        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
+      }
+      ldo = (int)(a.ldc >> 2);
+      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
+    }
+    const unsigned longmask = __ballot_sync(FULL, lng != 0);
+
+    // ---- runs of consecutive rows that are computed here (a queued long row ends a run)
+    int rb = 0;
+    while (rb < nrows) {
+      const unsigned lm = longmask >> rb;
+      const int re = lm ? rb + (__ffs(lm) - 1) : nrows;
+      if (re > rb) {
+        const int S = __shfl_sync(FULL, s, rb);
+        const int E = __shfl_sync(FULL, e, re - 1);
+        int cr = rb;
+        float4 acc[VEC][OV];
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+#pragma unroll
+          for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
+        auto store_row = [&]() {  // row cr <- acc, acc <- 0
+          float4* __restrict__ Cv = obase + (int64_t)cr * ldo;
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) {
+            if (colok[i]) {
+#pragma unroll
+              for (int h = 0; h < OV; ++h) {
+                float4* o = Cv + OV * (lane + 32 * i) + h;
+                float4 out;
+                if (t >= 0) out = acc[i][h];
+                else if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+                else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+                else out = acc[i][h];
+                __stcs(o, out);
+              }
+            }
+#pragma unroll
+            for (int h = 0; h < OV; ++h) acc[i][h] = Ops::zero();
+          }
+          ++cr;
+        };
+        // rows that end at non-zero index `pos` with nothing in them: written as zeros (acc is zero here)
+        auto skip_empty = [&](int pos) {
+          while (cr < re && __shfl_sync(FULL, e, cr) == pos) store_row();
+        };
+        skip_empty(S);
+
+        // (column, value) chunks of 32: [p0, p0+32) holds the batch being multiplied, the gathers run at most NS batches
+        // ahead (inside the first two chunks), the third chunk is the prefetch in flight
+        int p0 = S & ~31;
+        int c0 = 0, c1 = 0, c2 = 0;
+        float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+        {
+          const int i0 = p0 + lane, i1 = i0 + 32, i2 = i0 + 64;
+          if (i0 >= S && i0 < E) { c0 = __ldg(a.colind + i0); v0 = __ldg(a.val + i0); }
+          if (i1 < E) { c1 = __ldg(a.colind + i1); v1 = __ldg(a.val + i1); }
+          if (i2 < E) { c2 = __ldg(a.colind + i2); v2 = __ldg(a.val + i2); }
+        }
+        const int k0 = S >> 3, k1 = (E + 7) >> 3;  // batches [k0, k1): batch k = non-zeros [8k, 8k + 8)
+        // ---- gather of batch k: two tile::gather4 TMA copies (4 rows of B each, row ids straight from the column
+        // indices) into stage k % NS of the ring, completing on the stage's mbarrier.  Positions outside the run gather
+        // row 0 (never read back).
+        auto issue = [&](int k) {
+          if (k >= k1) return;
+          const int q0 = k << 3;
+          const int csel = (q0 - p0) >= 32 ? c1 : c0;
+          const int l0 = q0 & 31;
+          int r[G];
+#pragma unroll
+          for (int j = 0; j < G; ++j) {
+            const int cc = __shfl_sync(FULL, csel, l0 + j);
+            r[j] = (q0 + j >= S && q0 + j < E) ? cc : 0;
+          }
+          const unsigned slot = (gk + (unsigned)(k - k0)) % NS;
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier reads of the slot vs the copies into it
+          if (lane == 0) {
+            const uint32_t bar = bars_s + 8u * slot;
+            const uint32_t dst = ring_s + (slot * G) * rowb;
+            mbar_expect_tx(bar, (uint32_t)G * rowb);
+            tma_gather4(dst, &mapB, 0, r[0], r[1], r[2], r[3], bar);
+            tma_gather4(dst + 4u * rowb, &mapB, 0, r[4], r[5], r[6], r[7], bar);
+          }
+        };
+        // ---- multiply batch k in
+        auto consume = [&](int k) {
+          const int q0 = k << 3;
+          if (q0 - p0 >= 32) {  // consumed a chunk: shift, fetch the one after the next two
+            p0 += 32;
+            c0 = c1; v0 = v1; c1 = c2; v1 = v2;
+            const int i2 = p0 + 64 + lane;
+            c2 = 0; v2 = 0.f;
+            if (i2 < E) { c2 = __ldg(a.colind + i2); v2 = __ldg(a.val + i2); }
+          }
+          const unsigned g = gk + (unsigned)(k - k0);
+          const Raw* st = ring + (size_t)((g % NS) * G) * nvec;
+          float vv[G];
+#pragma unroll
+          for (int j = 0; j < G; ++j) vv[j] = __shfl_sync(FULL, v0, (q0 & 31) + j);
+          mbar_wait(bars_s + 8u * (g % NS), (g / NS) & 1u);
+          const int jlo = max(S - q0, 0), jhi = min(E - q0, G);
+          // rows whose last non-zero lies in this batch: bit j = "a row ends after non-zero q0 + j"
+          const unsigned epos = (unsigned)(e - 1 - q0);
+          const unsigned endmask = __reduce_or_sync(FULL, (lane < nrows && epos < (unsigned)G) ? (1u << epos) : 0u);
+          if (endmask == 0u && jlo == 0 && jhi == G) {
+            // whole batch inside one row (the common case): 8 x FMAs, no test
+#pragma unroll
+            for (int j = 0; j < G; ++j)
+#pragma unroll
+              for (int i = 0; i < VEC; ++i)
+                if (colok[i]) BV::fma(acc[i], vv[j], st[j * nvec + 32 * i]);
+          } else {
+            // one sweep per row piece [ja, jb): uniform branches around whole non-zeros, one copy of the row store
+            int ja = jlo;
+            while (ja < jhi) {
+              const unsigned em = endmask >> ja;
+              const bool ends = em != 0u && (ja + __ffs(em)) <= jhi;
+              const int jb = ends ? ja + __ffs(em) : jhi;
+#pragma unroll
+              for (int j = 0; j < G; ++j) {
+                if (j >= ja && j < jb) {
+#pragma unroll
+                  for (int i = 0; i < VEC; ++i)
+                    if (colok[i]) BV::fma(acc[i], vv[j], st[j * nvec + 32 * i]);
+                }
+              }
+              if (ends) {
+                store_row();
+                skip_empty(q0 + jb);
+              }
+              ja = jb;
+            }
+          }
+        };
+        for (int k = 0; k < NS; ++k) issue(k0 + k);
+        for (int k = k0; k < k1; ++k) {
+          consume(k);
+          __syncwarp();  // every lane is done reading the stage before it is refilled
+          issue(k + NS);
+        }
+        gk += (unsigned)(k1 - k0);
+        while (cr < re) store_row();  // trailing rows (only reached when the run holds no non-zero at all)
+      }
+      rb = re + 1;
+    }
+
+    if (t >= 0) {
+      __threadfence();
+      __syncwarp();
+      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
+      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
+      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
+      int last = 0;
+      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
+      last = __shfl_sync(FULL, last, 0);
+      if (last) {
+        __threadfence();
+        if (lane == 0) a.done[seg_slot] = 0;
+        float4 acc[VEC][OV];
+        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
+        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
+#pragma unroll
+          for (int i = 0; i < VEC; ++i)
+            if (colok[i]) {
+#pragma unroll
+              for (int h = 0; h < OV; ++h) {
+                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
+                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
+              }
+            }
+        }
+        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i)
+          if (colok[i]) {
+#pragma unroll
+            for (int h = 0; h < OV; ++h) {
+              float4* o = Cv + OV * (lane + 32 * i) + h;
+              float4 out;
+              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+              else out = acc[i][h];
+              __stcs(o, out);
+            }
+          }
+      }
+    } else {
+      item = __shfl_sync(FULL, next_item, 0);
+    }
+    pending = __shfl_sync(FULL, pending, 0);
+  }
+}
+
+
+
+template <int VEC, int NS, int WARPS, bool BF16>
+int launch_tma(const CsrArgs& a, int nsm, cudaStream_t st) {
+  CUtensorMap map;
+  // one box = one row of B (K elements); tile::gather4 fetches four of them per instruction
+  if (!make_map_rows(&map, BF16, a.B, (uint64_t)a.K, (uint64_t)a.b_rows, (uint64_t)a.ldb * (BF16 ? 2 : 4))) return SPMMDB_ERR_NOT_SUPPORTED;
+  const size_t rowb = (size_t)(a.K / (BF16 ? 8 : 4)) * 16;
+  const size_t smem = (size_t)WARPS * ((size_t)NS * 8 * rowb + 128);
+  auto kernel = csrmm_tma_kernel<VEC, NS, WARPS, BF16>;
+  SPMMDB_CUDA_OK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kernel<<<nsm, WARPS * 32, smem, st>>>(a, map);
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  kernel<<<nsm, WARPS * 32, smem, st>>>(a, map);  // sweep: segments queued late
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return SPMMDB_OK;
+}
+
+// ---------------------------------------------------------------------------
 // Async stream kernel (K % 4 == 0, K <= 256): same work distribution and the same per-element FMA
 // chain as csrmm_stream_kernel, but the B-row gathers are cp.async (LDGSTS) copies into a per-warp
 // shared-memory ring instead of loads into registers.  Every lane copies and later reads back only
@@ -1439,6 +1769,7 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
   a.m = m; a.K = K; a.rowptr = rowptr; a.colind = colind; a.val = val;
   a.B = B; a.ldb = ldb; a.C = C; a.ldc = ldc; a.alpha = alpha; a.beta = beta;
   a.b_bf16 = b_bf16; a.hot = hot;
+  a.b_rows = 0x7fffffff;  // the callee never learns k from gespmm_csrmm's signature; the map only bounds, never reads
   a.cold_policy = SPMMDB_TUNE("CSR_COLD_POLICY", 1);
   a.hot_policy = SPMMDB_TUNE("CSR_HOT_POLICY", 0);
   const int seg_override = current_segment_override();
@@ -1503,6 +1834,11 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     const int vec = (K / 8 + 31) / 32;
     const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
     const int bulk = SPMMDB_TUNE("CSR_LEAN", 1);  // 0: csrmm_stream_kernel, 1 / 2: csrmm_lean_kernel (two occupancies)
+    const int tma = SPMMDB_TUNE("CSR_TMA", 0);  // tile::gather4 ring kernel (rows of at most 256 elements)
+    if (tma && K <= 256) {
+      if (tma == 2) return launch_tma<1, 2, 16, true>(a, nsm, st);
+      return launch_tma<1, 4, 12, true>(a, nsm, st);
+    }
     if (bulk) {
       if (vec == 1) return bulk == 2 ? launch_lean<1, 4, true>(a, nsm, st) : launch_lean<1, 3, true>(a, nsm, st);
       if (vec == 2) return launch_lean<2, 2, true>(a, nsm, st);
@@ -1530,6 +1866,11 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     a.rpi = rpi;
     const int vec = (K / 4 + 31) / 32;
     const int bulk = SPMMDB_TUNE("CSR_LEAN", 1);  // 0: csrmm_stream_kernel, 1 / 2: csrmm_lean_kernel (two occupancies)
+    const int tma = SPMMDB_TUNE("CSR_TMA", 0);  // tile::gather4 ring kernel (rows of at most 256 elements)
+    if (tma && a.inline_segs && a.hot == nullptr && K <= 256) {
+      if (vec == 1) return tma == 2 ? launch_tma<1, 2, 16, false>(a, nsm, st) : launch_tma<1, 4, 12, false>(a, nsm, st);
+      return tma == 2 ? launch_tma<2, 4, 6, false>(a, nsm, st) : launch_tma<2, 2, 12, false>(a, nsm, st);
+    }
     if (bulk && a.inline_segs && a.hot == nullptr && vec <= 2) {
       if (vec == 1) return bulk == 2 ? launch_lean<1, 4, false>(a, nsm, st) : launch_lean<1, 3, false>(a, nsm, st);
       if (vec == 2) return launch_lean<2, 2, false>(a, nsm, st);

@@ -347,3 +347,37 @@ def test_csrmm_call_replays_correctly_from_a_cuda_graph(pkg, oracle, path):
         pkg.set_csrmm_segment(0)
         for knob in ("CSR_SMALL", "CSR_INLINE", "CSR_LEAN"):
             pkg.set_tuning(knob, None)
+
+
+# ----------------------------------------------------------------------------- tile::gather4 variant (opt-in)
+@pytest.mark.parametrize("K,bf16", [(256, False), (128, False), (64, False), (256, True), (128, True)])
+@pytest.mark.parametrize("mode", [1, 2])
+def test_tma_gather4_kernel_same_bits(pkg, oracle, K, bf16, mode):
+    """csrmm_tma_kernel (CSR_TMA knob): the B-row gather as cp.async.bulk.tensor tile::gather4 copies into a
+    shared-memory ring, the lean kernel's multiply loop -- same bits as the default kernel, alpha / beta included.
+    Measured slower than the register gather (profiles/r2n), so nothing selects it by default."""
+    rng, (rp, ci, v) = hub_matrix(600 + K)
+    m, k = rp.size - 1, 9000
+    B = rng.uniform(-1, 1, (k, K)).astype(np.float32)
+    C0 = rng.uniform(-1, 1, (m, K)).astype(np.float32)
+    dB = pkg.dense_pack_bf16(dev(B)) if bf16 else dev(B)
+    d = [dev(x) for x in (rp, ci, v)]
+    pkg.set_tuning("CSR_SMALL", 0)
+    pkg.set_tuning("CSR_INLINE", 1)
+    pkg.set_csrmm_segment(256)
+    try:
+        for alpha, beta in ((1.0, 0.0), (0.5, -2.0)):
+            ref, out = dev(C0), dev(C0)
+            pkg.csrmm_ex(*d, dB, ref, m, k, K, alpha=alpha, beta=beta)
+            pkg.set_tuning("CSR_TMA", mode)
+            pkg.csrmm_ex(*d, dB, out, m, k, K, alpha=alpha, beta=beta)
+            pkg.set_tuning("CSR_TMA", None)
+            assert torch.equal(ref, out), (alpha, beta)
+        if not bf16:
+            want = oracle.csrmm(rp, ci, v, B, K, C0=C0, alpha=0.5, beta=-2.0)
+            assert err_vs(oracle, out.cpu().numpy(), want, rp, ci, v, B, K, 0.5, -2.0, C0) <= TOL_FP32
+    finally:
+        pkg.set_tuning("CSR_TMA", None)
+        pkg.set_csrmm_segment(0)
+        pkg.set_tuning("CSR_SMALL", None)
+        pkg.set_tuning("CSR_INLINE", None)
