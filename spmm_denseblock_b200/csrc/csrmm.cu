@@ -861,12 +861,6 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
 }
 
 
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 
 // ---------------------------------------------------------------------------
@@ -1480,159 +1474,6 @@ int launch_tma(const CsrArgs& a, int nsm, cudaStream_t st) {
   return SPMMDB_OK;
 }
 
-// ---------------------------------------------------------------------------
-// Async stream kernel (K % 4 == 0, K <= 256): same work distribution and the same per-element FMA
-// chain as csrmm_stream_kernel, but the B-row gathers are cp.async (LDGSTS) copies into a per-warp
-// shared-memory ring instead of loads into registers.  Every lane copies and later reads back only
-// its own 16-byte columns, so the ring is private staging: no barrier, just cp.async.wait_group.
-// D batches of U rows are in flight per warp WHILE the previous batch is being multiplied -- the
-// register version has nothing in flight during its FMA phase and is capped by the register file
-// (ncu r1d: 123 registers, 16 warps/SM, 12.8 TB/s of gather with ~128 KB in flight per SM).  Here
-// 2 CTAs x 8 warps x D*U rows x K*4 B = 192 KB are in flight per SM.
-// Rows longer than `seg` are queued for csrmm_long_kernel; the item is then processed as the runs
-// of short rows between them.
-template <int VEC, int U, int D, int MINB>
-__global__ void __launch_bounds__(256, MINB) csrmm_async_kernel(const CsrArgs a_in) {
-  CsrArgs a = a_in;
-  a.epoch = __ldcg(a_in.epoch_dev);  // this call's number lives on the device: a captured CUDA graph replays correctly
-  static_assert(D * U + U <= 32, "issue pointer must stay inside the two staged (col, val) chunks");
-  using Ops = VecOps<float4>;
-  constexpr unsigned FULL = 0xffffffffu;
-  extern __shared__ __align__(16) float4 ring_all[];
-  const int lane = threadIdx.x & 31;
-  float4* ring = ring_all + (size_t)(threadIdx.x >> 5) * (D * U * VEC * 32) + lane;  // this lane's column of the ring
-  const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
-  const int nvec = a.K >> 2;
-  const int nitems = (a.m + a.rpi - 1) / a.rpi;
-  const float4* __restrict__ Bv = reinterpret_cast<const float4*>(a.B) + lane;
-  const int64_t ldbv = a.ldb >> 2;
-  bool colok[VEC];
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) colok[i] = (lane + 32 * i) < nvec;
-
-  int item = 0;
-  if (lane == 0) item = atomicAdd(a.counters + 3, 1);
-  item = __shfl_sync(FULL, item, 0);
-  while (item < nitems) {
-    int next_item = 0;
-    if (lane == 0) next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the loop
-
-    const int r0 = item * a.rpi;
-    const int nrows = min(a.rpi, a.m - r0);
-    int s = 0, e = 0;
-    if (lane < nrows) {
-      s = __ldg(a.rowptr + r0 + lane);
-      e = __ldg(a.rowptr + r0 + lane + 1);
-    }
-    int lng = (e - s) > a.seg;
-    if (__any_sync(FULL, lng)) {
-      if (lng) {
-        const int nseg = (e - s + a.seg - 1) / a.seg;
-        const int slot = atomicAdd(a.counters + 0, 1);
-        const int seg_base = atomicAdd(a.counters + 1, nseg);
-        if (slot >= a.cap_rows || seg_base + nseg > a.cap_segs) {
-          atomicExch(a.counters + 2, 1);
-          lng = 0;  // queue full (caller's nnz was too small): do the row here
-        } else {
-          a.long_rows[slot] = LongRow{r0 + lane, seg_base, nseg, a.epoch};
-          for (int t = 0; t < nseg; ++t) a.seg_owner[seg_base + t] = slot;
-        }
-      }
-    }
-    const uint32_t longmask = __ballot_sync(FULL, lng);
-
-    int rb = 0;
-    while (rb < nrows) {
-      const uint32_t lm = longmask >> rb;
-      const int re = lm ? rb + (__ffs(lm) - 1) : nrows;  // rows [rb, re) are short, row re (if any) is queued
-      if (re > rb) {
-        const int S = __shfl_sync(FULL, s, rb);
-        const int E = __shfl_sync(FULL, e, re - 1);
-        int cr = rb;                           // current output row (warp-uniform)
-        int ce = __shfl_sync(FULL, e, rb);     // its end in the non-zero stream
-        float4 acc[VEC];
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) acc[i] = Ops::zero();
-        auto flush_advance = [&]() {
-          float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)(r0 + cr) * (a.ldc >> 2) + lane;
-#pragma unroll
-          for (int i = 0; i < VEC; ++i) {
-            if (colok[i]) {
-              float4 out;
-              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i], a.beta, Cv[32 * i]);
-              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i]);
-              else out = acc[i];
-              __stcs(Cv + 32 * i, out);
-            }
-            acc[i] = Ops::zero();
-          }
-          ++cr;
-          ce = __shfl_sync(FULL, e, min(cr, 31));
-          if (cr >= re) ce = 0x7fffffff;
-        };
-
-        // two staged chunks of 32 (col, val) pairs: [p0, p0 + 32) and [p0 + 32, p0 + 64)
-        int p0 = S & ~31;
-        int c0 = 0, c1 = 0;
-        float v0 = 0.f, v1 = 0.f;
-        {
-          const int i0 = p0 + lane, i1 = p0 + 32 + lane;
-          if (i0 >= S && i0 < E) { c0 = __ldg(a.colind + i0); v0 = __ldg(a.val + i0); }
-          if (i1 < E) { c1 = __ldg(a.colind + i1); v1 = __ldg(a.val + i1); }
-        }
-        const int nb = (E - S + U - 1) / U;  // batches of U non-zeros, aligned to S
-        auto issue = [&](int b) {
-          if (b < nb) {
-            const uint32_t st = ring_s + (uint32_t)((b % D) * U) * (VEC * 32 * 16);
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-              const int q = S + b * U + u;
-              if (q < E) {
-                const int rel = q - p0;  // < 64 by the static_assert
-                const int cc = rel < 32 ? __shfl_sync(FULL, c0, rel) : __shfl_sync(FULL, c1, rel - 32);
-                const float4* __restrict__ brow = Bv + (int64_t)cc * ldbv;
-#pragma unroll
-                for (int i = 0; i < VEC; ++i)
-                  if (colok[i]) cp_async16(st + (uint32_t)((u * VEC + i) * 32 * 16), brow + 32 * i);
-              }
-            }
-          }
-          cp_async_commit();  // one group per call, empty or not: the wait below counts groups
-        };
-#pragma unroll
-        for (int b = 0; b < D; ++b) issue(b);
-        for (int b = 0; b < nb; ++b) {
-          cp_async_wait<D - 1>();
-          const float4* st = ring + (size_t)((b % D) * U) * (VEC * 32);
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int q = S + b * U + u;
-            if (q < E) {
-              if (q - p0 >= 32) {  // consumed the first chunk: shift, fetch the one after next
-                p0 += 32;
-                c0 = c1; v0 = v1;
-                const int i1 = p0 + 32 + lane;
-                c1 = 0; v1 = 0.f;
-                if (i1 < E) { c1 = __ldg(a.colind + i1); v1 = __ldg(a.val + i1); }
-              }
-              while (q >= ce) flush_advance();
-              const float vv = __shfl_sync(FULL, v0, q - p0);
-#pragma unroll
-              for (int i = 0; i < VEC; ++i)
-                if (colok[i]) Ops::fma(acc[i], vv, st[(u * VEC + i) * 32]);
-            }
-          }
-          issue(b + D);
-        }
-        cp_async_wait<0>();
-        while (cr < re) flush_advance();  // last row and trailing empty rows of the run
-      }
-      rb = re + 1;
-    }
-    item = __shfl_sync(FULL, next_item, 0);
-  }
-}
-
 template <typename V, int LPR, int VEC, int U>
 int launch_long(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   csrmm_long_kernel<V, LPR, VEC, U><<<long_ctas, 256, 0, st>>>(a);
@@ -1641,16 +1482,6 @@ int launch_long(const CsrArgs& a, int long_ctas, cudaStream_t st) {
   csrmm_reduce_kernel<V><<<nsm * 2, 256, 0, st>>>(a);
   SPMMDB_CUDA_OK(cudaGetLastError());
   return SPMMDB_OK;
-}
-
-template <int VEC, int U, int D, int MINB>
-int launch_async(const CsrArgs& a, int nsm, int long_ctas, cudaStream_t st) {
-  const size_t smem = (size_t)8 * D * U * VEC * 32 * sizeof(float4);
-  SPMMDB_CUDA_OK(cudaFuncSetAttribute(csrmm_async_kernel<VEC, U, D, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)smem));
-  csrmm_async_kernel<VEC, U, D, MINB><<<nsm * MINB, 256, smem, st>>>(a);
-  SPMMDB_CUDA_OK(cudaGetLastError());
-  return launch_long<float4, 32, VEC, 8>(a, long_ctas, st);
 }
 
 template <int VEC, int U, int MINB, bool BF16 = false>
@@ -1874,18 +1705,6 @@ int csrmm_rowmajor(int m, int K, int64_t nnz, const int* rowptr, const int* coli
     if (bulk && a.inline_segs && a.hot == nullptr && vec <= 2) {
       if (vec == 1) return bulk == 2 ? launch_lean<1, 4, false>(a, nsm, st) : launch_lean<1, 3, false>(a, nsm, st);
       if (vec == 2) return launch_lean<2, 2, false>(a, nsm, st);
-    }
-    const int async_env = SPMMDB_TUNE("CSR_ASYNC", 0);
-    if (async_env && vec <= 2) {
-      // ring per warp = D*U rows; 2 CTAs/SM x 8 warps x 12 KB = 192 KB in flight
-      if (vec == 1) {
-        if (async_env == 2) return launch_async<1, 4, 6, 2>(a, nsm, long_ctas, st);
-        if (async_env == 3) return launch_async<1, 4, 4, 3>(a, nsm, long_ctas, st);
-        return launch_async<1, 8, 3, 2>(a, nsm, long_ctas, st);
-      }
-      if (async_env == 2) return launch_async<2, 2, 6, 2>(a, nsm, long_ctas, st);
-      if (async_env == 3) return launch_async<2, 4, 2, 3>(a, nsm, long_ctas, st);
-      return launch_async<2, 4, 3, 2>(a, nsm, long_ctas, st);
     }
     const int variant = SPMMDB_TUNE("CSR_VARIANT", 0);
     if (vec == 1) {
