@@ -31,6 +31,7 @@ SIGNATURES = {
     "spmmdb_bsrmm_f32": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, c_i64, C.c_int, C.c_float, vp, vp, vp, vp,
                          c_i64, C.c_float, vp, c_i64, C.c_int, C.c_int, vp],
     "spmmdb_bsr_pack_bf16": [c_i64, C.c_int, vp, vp, vp],
+    "spmmdb_bsr_transpose_blocks_f32": [c_i64, C.c_int, vp, vp, vp],
     "spmmdb_block_gemm_f32": [C.c_int, C.c_int, c_i64, C.c_int, vp, vp, vp, vp, vp, C.c_int, vp],
     "spmmdb_csr2bsr_nnz": [C.c_int, C.c_int, vp, vp, C.c_int, vp, C.POINTER(C.c_int), vp],
     "spmmdb_csr2bsr_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp, vp, vp, vp],

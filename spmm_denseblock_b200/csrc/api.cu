@@ -16,6 +16,7 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
 bool bsrmm_tc_supported(int trans_b, int n, int bs, int64_t ldb, const float* B, const float* val, int c_layout,
                         int64_t ldc, const float* C);
 int bsr_pack_bf16(int64_t elems, const float* in, void* out, cudaStream_t st);
+int bsr_transpose_blocks(int64_t nnzb, int bs, const float* in, float* out, cudaStream_t st);
 
 namespace {
 
@@ -165,4 +166,12 @@ extern "C" int spmmdb_bsr_pack_bf16(int64_t nnzb, int block_dim, const float* bs
   if (((uintptr_t)bsr_val | (uintptr_t)out_bf16) % 16 != 0) return SPMMDB_ERR_INVALID_VALUE;
   if (device_sm() < 0) return SPMMDB_ERR_CUDA;
   return bsr_pack_bf16(nnzb * block_dim * block_dim, bsr_val, out_bf16, (cudaStream_t)stream);
+}
+
+extern "C" int spmmdb_bsr_transpose_blocks_f32(int64_t nnzb, int block_dim, const float* bsr_val, float* out, void* stream) {
+  if (nnzb < 0 || block_dim <= 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (nnzb == 0) return SPMMDB_OK;
+  if (bsr_val == nullptr || out == nullptr || bsr_val == out) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  return bsr_transpose_blocks(nnzb, block_dim, bsr_val, out, (cudaStream_t)stream);
 }

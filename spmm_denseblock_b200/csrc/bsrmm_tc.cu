@@ -875,6 +875,17 @@ int bsrmm_tc(int dir, int trans_b, int mb, int n, int kb, int64_t nnzb, int bs, 
   return launch_tc<false, 3>(a, mapB, mapA, grid, smem_bytes, st);
 }
 
+// column-major blocks <-> row-major blocks, once per matrix (spmmdb_bsr_transpose_blocks_f32)
+int bsr_transpose_blocks(int64_t nnzb, int bs, const float* in, float* out, cudaStream_t st) {
+  const int64_t elems = nnzb * bs * bs;
+  if (elems > 0) {
+    int blocks = (int)((elems + 255) / 256 < 148 * 16 ? (elems + 255) / 256 : 148 * 16);
+    block_transpose_kernel<<<blocks, 256, 0, st>>>(in, out, bs, nnzb);
+    SPMMDB_CUDA_OK(cudaGetLastError());
+  }
+  return SPMMDB_OK;
+}
+
 int bsr_pack_bf16(int64_t elems, const float* in, void* out, cudaStream_t st) {
   const int64_t n4 = elems / 4;
   if (n4 > 0) {

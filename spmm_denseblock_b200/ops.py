@@ -133,6 +133,16 @@ def rocsparse_bsrmm(direction, trans_A, trans_B, mb, n, kb, nnzb, alpha, bsr_val
                                   math, _stream())
 
 
+def bsr_transpose_blocks(bsr_val, block_dim):
+    """Column-major blocks -> row-major blocks (or back), once per matrix: spmmdb_bsr_transpose_blocks_f32."""
+    _dev(bsr_val)
+    out = torch.empty_like(bsr_val)
+    nnzb = bsr_val.numel() // (block_dim * block_dim)
+    check(lib().spmmdb_bsr_transpose_blocks_f32(nnzb, block_dim, _p(bsr_val), _p(out), _stream()),
+          "spmmdb_bsr_transpose_blocks_f32")
+    return out
+
+
 def block_gemm(mb, dim, nnzb, block_dim, bsr_rowptr, bsr_colind, bsr_val, Y, Z, math=MATH_FP32):
     _dev(bsr_rowptr, bsr_colind, bsr_val, Y, Z)
     rc = lib().spmmdb_block_gemm_f32(mb, dim, nnzb, block_dim, _p(bsr_rowptr), _p(bsr_colind), _p(bsr_val), _p(Y),

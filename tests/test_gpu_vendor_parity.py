@@ -209,3 +209,24 @@ def test_csrmm_vs_cusparse_spmm(pkg, cmp, K, layouts):
     cmp.cusparse_spmm(m, k, K, *d, theirs, alg=0, b_layout=b_layout, c_layout=c_layout, alpha=1.5, beta=-0.5)
     torch.cuda.synchronize()
     assert float((ours - theirs).abs().max()) <= 2e-4
+
+
+@pytest.mark.parametrize("bs", [16, 32, 5])
+def test_transpose_blocks_once_equals_direction_column(pkg, bs):
+    """spmmdb_bsr_transpose_blocks_f32: column-major blocks converted once + SPMMDB_DIR_ROW give the bits of the
+    SPMMDB_DIR_COLUMN call (which transposes per call on the tf32 path); twice = identity."""
+    rng = np.random.default_rng(bs)
+    mb, n = 30, 128
+    brp, bci, bv = random_bsr(rng, mb, mb, bs, 5)
+    d_rp, d_ci, d_v = dev(brp), dev(bci), dev(bv)
+    rowmajor = pkg.bsr_transpose_blocks(d_v, bs)
+    assert torch.equal(pkg.bsr_transpose_blocks(rowmajor, bs), d_v)
+    want = torch.from_numpy(bv.reshape(-1, bs, bs).transpose(0, 2, 1).copy().reshape(-1)).cuda()
+    assert torch.equal(rowmajor, want)
+    B = dev(rng.uniform(-1, 1, (mb * bs, n)).astype(np.float32))
+    for math in (0, 1):
+        c1 = torch.zeros(n, mb * bs, device="cuda")
+        c2 = torch.zeros(n, mb * bs, device="cuda")
+        pkg.bsrmm(1, 1, mb, n, mb, bci.size, 1.0, d_v, d_rp, d_ci, bs, B, n, 0.0, c1, mb * bs, math=math)
+        pkg.bsrmm(0, 1, mb, n, mb, bci.size, 1.0, rowmajor, d_rp, d_ci, bs, B, n, 0.0, c2, mb * bs, math=math)
+        assert torch.equal(c1, c2), math
