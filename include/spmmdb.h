@@ -280,6 +280,31 @@ int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr,
                           void* stream);
 
 /* --------------------------------------------------------------------------
+ * Allocation-free CSR x dense:  C = alpha * A * B + beta * C, row-major B (ld >= K) and C (ld >= K).
+ * No counterpart in the reference: added for callers that cannot
+ * have the library call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  The entry point calls no cudaMalloc / cudaFree and no allocating library routine: the scratch
+ * its kernels need (long-row list, per-segment partial sums) is one fixed __device__ array inside the
+ * library, SPMMDB_NOALLOC_SCRATCH_BYTES per GPU that loads libspmmdb.so, held until the process exits.
+ *   limit     K <= SPMMDB_NOALLOC_MAX_K; a larger K returns SPMMDB_ERR_NOT_SUPPORTED and spmmdb_last_error()
+ *             names the limit.  m, k and nnz are not limited: long rows beyond the array's capacity
+ *             (16384 rows of more than 1024 non-zeros, min(16384, 2^21 / K) segments of 512 non-zeros) are
+ *             summed in place, with the same result.
+ *   sharing   every call on a device uses the same array and finds the last call's contents in it (the
+ *             entry point clears what must start at zero).  Calls on one stream are ordered by the stream;
+ *             calls that OVERLAP on the GPU (two streams, two host threads) race on the array and give
+ *             wrong sums: serialise them.
+ *   result    within 1e-5 of spmmdb_csrmm_f32; rows of <= 1024 non-zeros are the same FMA chain in CSR
+ *             order, longer rows are summed per 512-entry segment, segment sums added in order.
+ *   val must not be NULL; asynchronous on `stream`.
+ * ------------------------------------------------------------------------ */
+#define SPMMDB_NOALLOC_MAX_K 512
+#define SPMMDB_NOALLOC_SCRATCH_BYTES 8782080
+int spmmdb_csrmm_noalloc_f32(int m, int k, int K, const int* rowptr, const int* colind, const float* val,
+                             const float* B, int64_t ldb, float* C, int64_t ldc, float alpha, float beta,
+                             void* stream);
+
+/* --------------------------------------------------------------------------
  * Multi-GPU row sharding (new behaviour defined by BASELINE.json; the reference
  * is single-GPU).  HOST function, no CUDA call: splits the rows of a CSR (or
  * block rows of a BSR) matrix into `parts` contiguous ranges of ~equal nnz.

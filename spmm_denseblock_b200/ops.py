@@ -101,6 +101,16 @@ def csrmm_ex(rowptr, colind, val, B, C_out, m, k, K, ldb=None, ldc=None, alpha=1
     return C_out
 
 
+def csrmm_noalloc(rowptr, colind, val, B, C_out, m, k, K, ldb=None, ldc=None, alpha=1.0, beta=0.0):
+    """spmmdb_csrmm_noalloc_f32: row-major CSR x dense whose scratch is a fixed device array inside the library
+    (no cudaMalloc in the call; K <= 512; calls that overlap on the GPU race on the array)."""
+    _dev(rowptr, colind, val, B, C_out)
+    rc = lib().spmmdb_csrmm_noalloc_f32(m, k, K, _p(rowptr), _p(colind), _p(val), _p(B), K if ldb is None else ldb,
+                                        _p(C_out), K if ldc is None else ldc, alpha, beta, _stream())
+    check(rc, "spmmdb_csrmm_noalloc_f32")
+    return C_out
+
+
 def gespmm_csrmm(A_nrows, B_ncols, A_rowPtr, A_colInd, A_val, B, C_out):
     """gespmm_csrmm<float>(A_nrows, B_ncols, rowPtr, colInd, val, B, C): row-major B/C,
     alpha=1, beta=0, nnz unknown to the callee (gespmm_csrmm.h:422-426)."""
