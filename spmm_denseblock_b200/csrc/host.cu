@@ -7,6 +7,19 @@
 
 using namespace spmmdb;
 
+// Column widths of the feature slabs of one call (at most 16, each a multiple of 16 columns); returns their number.
+static int plan_slabs(int K, int slabs_knob, int tail, int* widths) {
+  int main_w = 64;
+  if (slabs_knob > 0) main_w = (K % slabs_knob == 0 && (K / slabs_knob) % 16 == 0) ? K / slabs_knob : K;
+  if (K % 16 != 0 || main_w >= K) { widths[0] = K; return 1; }
+  if (tail < 16 || tail % 16 != 0) tail = main_w;
+  int n = 0, left = K;
+  while (left > main_w && n < 12) { widths[n++] = main_w; left -= main_w; }               // full-width slabs
+  while (n < 15 && left >= 2 * tail && (left / 2) % 16 == 0) { widths[n++] = left / 2; left -= left / 2; }  // halves
+  widths[n++] = left;
+  return n;
+}
+
 extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int* h_rowptr, const int* h_colind,
                                      const float* h_val, const float* h_B, float* h_C, float alpha, float beta,
                                      void* stream) {
@@ -35,9 +48,11 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   // Feature slabs: columns [c0, c0 + Ks) of C need only the same columns of B, so the host<->device copies of one
   // slab overlap the kernel and the opposite-direction copy of its neighbours (PCIe is full duplex): the call costs
   // about H2D(A) + H2D(B) + D2H(one slab) instead of H2D(A) + H2D(B) + kernel + D2H(C).
-  const int slabs_env = SPMMDB_TUNE("HOST_SLABS", 0);
-  int slabs = slabs_env > 0 ? slabs_env : 4;
-  while (slabs > 1 && (K % slabs != 0 || (K / slabs) % 64 != 0)) slabs >>= 1;  // >= 256-byte rows for the DMA engines
+  // The call ends with the D2H copy of the LAST slab alone on the wire, so the slabs shrink towards the end:
+  // 64-column slabs (HOST_SLABS > 0: K / HOST_SLABS columns), then the rest halved down to HOST_TAIL columns
+  // (K = 256: 64 64 64 32 16 16; rows narrower than 64 bytes are not worth a DMA descriptor each).
+  int widths[16];
+  const int slabs = plan_slabs(K, SPMMDB_TUNE("HOST_SLABS", 0), SPMMDB_TUNE("HOST_TAIL", 16), widths);
   if (slabs <= 1) {
     SPMMDB_CUDA_OK(cudaMemcpyAsync(dB, h_B, b_bytes, cudaMemcpyHostToDevice, st));
     if (beta != 0.f) SPMMDB_CUDA_OK(cudaMemcpyAsync(dC, h_C, c_bytes, cudaMemcpyHostToDevice, st));
@@ -52,7 +67,6 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   static thread_local cudaStream_t s_run = nullptr, s_out = nullptr;
   static thread_local cudaEvent_t ev_in[16], ev_run[16];
   static thread_local bool ev_made = false;
-  if (slabs > 16) slabs = 16;
   if (s_run == nullptr) {
     SPMMDB_CUDA_OK(cudaStreamCreateWithFlags(&s_run, cudaStreamNonBlocking));
     SPMMDB_CUDA_OK(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
@@ -64,14 +78,15 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
     }
     ev_made = true;
   }
-  const int Ks = K / slabs;
-  const size_t pitch = sizeof(float) * (size_t)K, width = sizeof(float) * (size_t)Ks;
+  const size_t pitch = sizeof(float) * (size_t)K;
   // the kernels of all slabs share the whole call's segment length (same bits as the one-shot call)
   const int seg_now = current_segment_override();
   ScopedSegment pin(seg_now ? seg_now : spmmdb_csrmm_segment_for(m, nnz));
   int rc = SPMMDB_OK;
-  for (int sl = 0; sl < slabs && rc == SPMMDB_OK; ++sl) {
-    const size_t off = (size_t)sl * Ks;
+  size_t off = 0;
+  for (int sl = 0; sl < slabs && rc == SPMMDB_OK; off += widths[sl], ++sl) {
+    const int Ks = widths[sl];
+    const size_t width = sizeof(float) * (size_t)Ks;
     cudaError_t e = cudaMemcpy2DAsync(dB + off, pitch, h_B + off, pitch, width, (size_t)k, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess && beta != 0.f)
       e = cudaMemcpy2DAsync(dC + off, pitch, h_C + off, pitch, width, (size_t)m, cudaMemcpyHostToDevice, st);

@@ -414,7 +414,8 @@ def test_csrmm_understated_nnz_overflows_the_long_row_queue(pkg, oracle, K, alph
         assert err <= TOL_FP32, (nnz, err)
 
 
-@pytest.mark.parametrize("K,alpha,beta", [(256, 1.0, 0.0), (256, 0.5, 2.0), (128, 1.0, 0.0), (100, 1.0, 0.0)])
+@pytest.mark.parametrize("K,alpha,beta", [(256, 1.0, 0.0), (256, 0.5, 2.0), (128, 1.0, 0.0), (100, 1.0, 0.0), (192, 1.0, 0.0),
+                                          (1024, 1.0, -1.0), (80, 1.0, 0.0)])
 def test_csrmm_host_entry_slab_pipeline(pkg, oracle, K, alpha, beta):
     """spmmdb_csrmm_host_f32 (host buffers; feature slabs copied / computed / copied back in a pipeline when
     K allows) returns the bits of the device call on the same inputs."""
@@ -584,14 +585,22 @@ def test_permute_golden_reference(pkg, golden_dir):
     assert np.array_equal(nrp.cpu().numpy(), d["p_rowptr"]) and np.array_equal(nci.cpu().numpy(), d["p_colind"])
 
 
+@pytest.mark.parametrize("key64", [0, 1])
 @pytest.mark.parametrize("n,avg,hubs", [(700, 5, {}), (3000, 20, {5: 40, 9: 1000, 11: 1025, 77: 2999}),
+                                        (9000, 12, {2: 32, 3: 33, 10: 128, 11: 129, 20: 512, 21: 513, 30: 4096,
+                                                    31: 4097, 40: 2048, 41: 8192, 42: 8999, 43: 1024}),
                                         (40000, 3, {123: 16384, 9000: 16385, 39999: 33000})])
-def test_permute_csr_bit_exact_with_values(pkg, oracle, n, avg, hubs):
-    """All row-length classes (warp, shared-memory CTA small / large, global staging), values follow entries."""
+def test_permute_csr_bit_exact_with_values(pkg, oracle, n, avg, hubs, key64):
+    """All row-length classes (warp with 1 / 4 / 16 keys per lane, shared-memory CTA small / large, global staging)
+    and both key widths; values follow entries."""
     rng = np.random.default_rng(n)
     rp, ci, v = random_csr(rng, n, n, avg, hubs=hubs, empty_rows={1, n - 1})
     perm = rng.permutation(n).astype(np.int32)
-    nrp, nci, nv = pkg.permute_csr(dev(rp), dev(ci), dev(v), dev(perm))
+    pkg.set_tuning("PERM_KEY64", key64)
+    try:
+        nrp, nci, nv = pkg.permute_csr(dev(rp), dev(ci), dev(v), dev(perm))
+    finally:
+        pkg.set_tuning("PERM_KEY64", None)
     orp, oci = oracle.permutate_csr(rp, ci, perm)
     assert np.array_equal(nrp.cpu().numpy(), orp) and np.array_equal(nci.cpu().numpy(), oci)
     # values: A'[perm[i], perm[j]] == A[i, j]
