@@ -48,11 +48,13 @@ extern "C" int spmmdb_csrmm_host_f32(int m, int k, int K, int64_t nnz, const int
   // Feature slabs: columns [c0, c0 + Ks) of C need only the same columns of B, so the host<->device copies of one
   // slab overlap the kernel and the opposite-direction copy of its neighbours (PCIe is full duplex): the call costs
   // about H2D(A) + H2D(B) + D2H(one slab) instead of H2D(A) + H2D(B) + kernel + D2H(C).
-  // The call ends with the D2H copy of the LAST slab alone on the wire, so the slabs shrink towards the end:
-  // 64-column slabs (HOST_SLABS > 0: K / HOST_SLABS columns), then the rest halved down to HOST_TAIL columns
-  // (K = 256: 64 64 64 32 16 16; rows narrower than 64 bytes are not worth a DMA descriptor each).
+  // The call ends with the D2H copy of the LAST slab alone on the wire.  Slabs are 64 columns wide (HOST_SLABS > 0:
+  // K / HOST_SLABS columns): narrower last slabs (HOST_TAIL = 32 / 16: the rest of K halved down to that width) shorten
+  // that tail but lose more in the strided copies than they gain -- rows under 256 bytes run the DMA engines well
+  // below the PCIe rate (products-shaped graph, K = 256: 74.1 ms with 64 64 64 64, 79.1 ms with 64 64 64 32 32,
+  // 89.8 ms with 64 64 64 32 16 16; profiles/r2q_host_slabs.jsonl).
   int widths[16];
-  const int slabs = plan_slabs(K, SPMMDB_TUNE("HOST_SLABS", 0), SPMMDB_TUNE("HOST_TAIL", 16), widths);
+  const int slabs = plan_slabs(K, SPMMDB_TUNE("HOST_SLABS", 0), SPMMDB_TUNE("HOST_TAIL", 64), widths);
   if (slabs <= 1) {
     SPMMDB_CUDA_OK(cudaMemcpyAsync(dB, h_B, b_bytes, cudaMemcpyHostToDevice, st));
     if (beta != 0.f) SPMMDB_CUDA_OK(cudaMemcpyAsync(dC, h_C, c_bytes, cudaMemcpyHostToDevice, st));
