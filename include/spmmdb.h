@@ -270,6 +270,23 @@ int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* coli
                                 int64_t* dist10_host, void* stream);
 
 /* --------------------------------------------------------------------------
+ * The reference's two simple orderings produced on the device.  Both write the permutation
+ * old2new[n] (DEVICE) that spmmdb_permute_csr_f32 / spmmdb_permute_rows_f32 apply; both synchronise `stream`.
+ *   spmmdb_order_by_degree  maxDegreeSort (reorder_strategy.cc:41-55): descending degree.  The reference leaves
+ *                           equal degrees in whatever order std::sort gives; here ties keep ascending id, so the
+ *                           permuted graph has the reference's row lengths always, its rows when degrees differ.
+ *   spmmdb_order_bfs        BFSTraversal (reorder_strategy.cc:68-98): FIFO breadth-first numbering, started at the
+ *                           lowest unvisited id, neighbours in adjacency order (colind need not be sorted; feed
+ *                           lists sorted by descending degree for reverseCuthillMcKee, :57-66).  The reference's
+ *                           permutation exactly, for a symmetric pattern (undirected graph); a pattern where the
+ *                           search from a component's lowest id does not reach the whole weakly connected
+ *                           component returns SPMMDB_ERR_NOT_SUPPORTED.
+ * The other front-ends (Gorder, Rabbit, METIS, greedy) stay on the CPU (BASELINE.json north_star).
+ * ------------------------------------------------------------------------ */
+int spmmdb_order_by_degree(int n, const int* rowptr, int* old2new, void* stream);
+int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int* old2new, void* stream);
+
+/* --------------------------------------------------------------------------
  * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all
  * pointers are HOST pointers (pinned memory gives full PCIe rate).  Copies A and
  * B to the device, runs the device path, copies C back and synchronises -- the

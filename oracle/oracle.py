@@ -178,6 +178,28 @@ def permutate_csr(rowptr, colind, old2new):
     return nrp, nci[:colind.size]
 
 
+def bfs_order(rowptr, colind):
+    """old2new of BFSTraversal (reorder_strategy.cc:68-98); colind in adjacency order."""
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    out = np.zeros(max(n, 1), np.int32)
+    f = lib().oracle_bfs_order
+    f.argtypes = [C.c_int, _i32p, _i32p, _i32p]
+    f(n, rowptr, colind if colind.size else np.zeros(1, np.int32), out)
+    return out[:n]
+
+
+def degree_order(rowptr):
+    """old2new of maxDegreeSort (reorder_strategy.cc:41-55), equal degrees in ascending id."""
+    rowptr = _i32(rowptr)
+    n = rowptr.size - 1
+    out = np.zeros(max(n, 1), np.int32)
+    f = lib().oracle_degree_order
+    f.argtypes = [C.c_int, _i32p, _i32p]
+    f(n, rowptr, out)
+    return out[:n]
+
+
 def calculate_nnzb(rowptr, colind, bs):
     rowptr, colind = _i32(rowptr), _i32(colind)
     f = lib().oracle_calculate_nnzb
@@ -314,6 +336,28 @@ def ref_rcmk_graph(rowptr, colind):
     L.ref_rcmk_graph.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p]
     L.ref_rcmk_graph(n, rowptr, colind, nrp, nci)
     return nrp, nci[:colind.size]
+
+
+def _ref_graph_call(name, rowptr, colind):
+    L = ref_host_lib()
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    nrp = np.zeros(n + 1, np.int32)
+    nci = np.zeros(max(colind.size, 1), np.int32)
+    f = getattr(L, name)
+    f.argtypes = [C.c_int, _i32p, _i32p, _i32p, _i32p]
+    f(n, rowptr, colind, nrp, nci)
+    return nrp, nci[:colind.size]
+
+
+def ref_bfs_graph(rowptr, colind):
+    """The reference's own BFSTraversal (reorder_strategy.cc:68-98): returns the REORDERED graph."""
+    return _ref_graph_call("ref_bfs_graph", rowptr, colind)
+
+
+def ref_max_degree_sort_graph(rowptr, colind):
+    """The reference's own maxDegreeSort (reorder_strategy.cc:41-55): returns the REORDERED graph."""
+    return _ref_graph_call("ref_max_degree_sort_graph", rowptr, colind)
 
 
 _ref_divide = None

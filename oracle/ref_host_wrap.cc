@@ -43,6 +43,15 @@ void ref_rcmk_graph(int n, const int* rowptr, const int* colind, int* new_rowptr
   from_adj(reverseCuthillMcKee(to_adj(n, rowptr, colind)), new_rowptr, new_colind);
 }
 
+// BFSTraversal (reorder_strategy.cc:68-98) and maxDegreeSort (:41-55): the reordered graphs
+void ref_bfs_graph(int n, const int* rowptr, const int* colind, int* new_rowptr, int* new_colind) {
+  from_adj(BFSTraversal(to_adj(n, rowptr, colind)), new_rowptr, new_colind);
+}
+
+void ref_max_degree_sort_graph(int n, const int* rowptr, const int* colind, int* new_rowptr, int* new_colind) {
+  from_adj(maxDegreeSort(to_adj(n, rowptr, colind)), new_rowptr, new_colind);
+}
+
 void ref_dump_csr(const char* prefix, int n, int nnz, int* rowptr, int* colind) {
   dumpCSRToFile(prefix, n, nnz, rowptr, colind);              // load_data.cc:125-141
 }

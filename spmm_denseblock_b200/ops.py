@@ -268,6 +268,24 @@ def permute_csr(rowptr, colind, val, old2new):
     return nrp, nci, nv
 
 
+def order_by_degree(rowptr):
+    """old2new of maxDegreeSort (reorder_strategy.cc:41-55): descending degree, ties by ascending id."""
+    _dev(rowptr)
+    n = rowptr.numel() - 1
+    old2new = torch.empty(n, dtype=torch.int32, device=rowptr.device)
+    check(lib().spmmdb_order_by_degree(n, _p(rowptr), _p(old2new), _stream()), "spmmdb_order_by_degree")
+    return old2new
+
+
+def order_bfs(rowptr, colind):
+    """old2new of BFSTraversal (reorder_strategy.cc:68-98) for a symmetric pattern; colind in adjacency order."""
+    _dev(rowptr, colind)
+    n = rowptr.numel() - 1
+    old2new = torch.empty(n, dtype=torch.int32, device=rowptr.device)
+    check(lib().spmmdb_order_bfs(n, _p(rowptr), _p(colind), _p(old2new), _stream()), "spmmdb_order_bfs")
+    return old2new
+
+
 def permute_rows(X, old2new):
     """out[old2new[r]] = X[r] for a row-major dense matrix."""
     _dev(X, old2new)

@@ -664,6 +664,86 @@ def test_permute_full_size_products_property(pkg):
     assert torch.equal(brp, rp) and torch.equal(bci, ci)
 
 
+# ----------------------------------------------------------------------------- orderings produced on the device
+def _order_cases():
+    from helpers import undirected_graph
+    rng = np.random.default_rng(21)
+    yield "components+isolated+hub+loops+duplicates", undirected_graph(
+        rng, 5000, 4, components=9, isolated=(0, 17, 4999), hubs={3: 1500, 40: 300}, self_loops=20, duplicates=30)
+    yield "unsorted adjacency lists", undirected_graph(rng, 3000, 5, components=2, shuffle_rows=True)
+    yield "all isolated", (np.zeros(258, np.int32), np.zeros(0, np.int32))
+    path = np.arange(1500)
+    rp = np.zeros(1501, np.int32)
+    rp[1:] = np.cumsum(np.where((path == 0) | (path == 1499), 1, 2))
+    ci = np.concatenate([[1]] + [[i - 1, i + 1] for i in range(1, 1499)] + [[1498]]).astype(np.int32)
+    yield "path (one level per vertex)", (rp, ci)
+    yield "many small components", undirected_graph(rng, 20000, 2.2, components=4000)
+
+
+@pytest.mark.parametrize("name,graph", list(_order_cases()), ids=lambda x: x if isinstance(x, str) else "")
+def test_order_bfs_is_the_reference_permutation(pkg, oracle, name, graph):
+    """spmmdb_order_bfs == BFSTraversal (reorder_strategy.cc:68-98): the permutation equals the sequential
+    restatement's, and the graph permuted with it on the device equals the reference's own output graph."""
+    rp, ci = graph
+    p = pkg.order_bfs(dev(rp), dev(ci))
+    assert np.array_equal(p.cpu().numpy(), oracle.bfs_order(rp, ci))
+    if ci.size and oracle.ref_host_lib() is not None and hasattr(oracle.ref_host_lib(), "ref_bfs_graph"):
+        nrp, nci, _ = pkg.permute_csr(dev(rp), dev(ci), None, p)
+        wrp, wci = oracle.ref_bfs_graph(rp, ci)
+        assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
+
+
+def test_order_bfs_config_shapes_and_refusal(pkg, oracle):
+    """The C2-shaped graph symmetrised (169 343 vertices) and the C4 batch of molecule graphs (tens of thousands of
+    components) against the sequential restatement; a pattern that is not symmetric is refused."""
+    import ctypes as C
+
+    import scipy.sparse as sp
+    from spmm_denseblock_b200 import graphs
+    for cfg, scale in (("c2_arxiv", 1.0), ("c4_molhiv", 0.25)):
+        rp, ci = graphs.make_config_graph(cfg, device="cuda", scale=scale)
+        rp, ci = rp.cpu().numpy(), ci.cpu().numpy()
+        n = rp.size - 1
+        A = sp.csr_matrix((np.ones(ci.size, np.int8), ci, rp), shape=(n, n))
+        A = ((A + A.T) > 0).astype(np.int8).tocsr()
+        A.sort_indices()
+        rp, ci = A.indptr.astype(np.int32), A.indices.astype(np.int32)
+        p = pkg.order_bfs(dev(rp), dev(ci)).cpu().numpy()
+        assert np.array_equal(p, oracle.bfs_order(rp, ci)), cfg
+    rp = np.array([0, 0, 1, 1], np.int32)  # 1 -> 0 only: the search from vertex 0 never reaches vertex 1
+    ci = np.array([0], np.int32)
+    out = torch.empty(3, dtype=torch.int32, device="cuda")
+    rc = pkg.lib().spmmdb_order_bfs(3, C.c_void_p(dev(rp).data_ptr()), C.c_void_p(dev(ci).data_ptr()),
+                                    C.c_void_p(out.data_ptr()), C.c_void_p(0))
+    assert rc == -2 and b"not symmetric" in pkg.lib().spmmdb_last_error()
+
+
+def test_order_by_degree(pkg, oracle):
+    """spmmdb_order_by_degree == maxDegreeSort (reorder_strategy.cc:41-55) with ties in ascending id: the
+    restatement's permutation exactly; the reference's row lengths always, its rows when all degrees differ."""
+    rng = np.random.default_rng(8)
+    rp, ci, _ = random_csr(rng, 30000, 30000, 6, hubs={5: 9000, 77: 20000, 29999: 513}, empty_rows={0, 9, 29998})
+    q = pkg.order_by_degree(dev(rp))
+    assert np.array_equal(q.cpu().numpy(), oracle.degree_order(rp))
+    has_ref = oracle.ref_host_lib() is not None and hasattr(oracle.ref_host_lib(), "ref_max_degree_sort_graph")
+    if has_ref:
+        nrp, _, _ = pkg.permute_csr(dev(rp), dev(ci), None, q)
+        assert np.array_equal(nrp.cpu().numpy(), oracle.ref_max_degree_sort_graph(rp, ci)[0])
+    n = 700
+    degs = rng.permutation(n)
+    rows = [np.sort(rng.choice(n, size=d, replace=False)) for d in degs]
+    rp = np.zeros(n + 1, np.int32)
+    rp[1:] = np.cumsum(degs)
+    ci = np.concatenate(rows).astype(np.int32)
+    q = pkg.order_by_degree(dev(rp))
+    assert np.array_equal(q.cpu().numpy(), oracle.degree_order(rp))
+    if has_ref:
+        nrp, nci, _ = pkg.permute_csr(dev(rp), dev(ci), None, q)
+        wrp, wci = oracle.ref_max_degree_sort_graph(rp, ci)
+        assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
+    assert pkg.order_by_degree(dev(np.zeros(5, np.int32))).cpu().tolist() == [0, 1, 2, 3]
+
+
 @pytest.mark.parametrize("bs", [2, 3, 4, 8, 16, 32, 64])
 def test_block_fill_histogram_divide_metrics_bit_exact(pkg, oracle, bs):
     """spmmdb_block_fill_histogram == calculate_block_density_dist (block_density_dist.cpp:47-86), every decile,

@@ -193,3 +193,39 @@ def test_block_density_dist_restatement_matches_the_reference(oracle):
         rp, ci, _ = random_csr(rng, n, n, avg)
         for bs in (2, 3, 4, 8, 16, 32):
             assert np.array_equal(oracle.block_density_dist(rp, ci, bs), oracle.ref_block_density_dist(rp, ci, bs))
+
+
+def test_bfs_and_degree_order_restatements_match_the_reference(oracle):
+    """oracle.bfs_order / degree_order against the reference's own BFSTraversal / maxDegreeSort
+    (reorder_strategy.cc:41-98, compiled into oracle/_ref/libref_host.so).  The reference returns the reordered
+    graph, so the restated permutation is applied with the (golden-pinned) permutate restatement and the graphs
+    are compared.  maxDegreeSort leaves equal degrees in std::sort's order: row lengths always agree, the rows
+    themselves when all degrees differ."""
+    if oracle.ref_host_lib() is None or not hasattr(oracle.ref_host_lib(), "ref_bfs_graph"):
+        pytest.skip("oracle/_ref/libref_host.so not built")
+    from helpers import random_csr, undirected_graph
+    rng = np.random.default_rng(11)
+    cases = [undirected_graph(rng, 500, 4, components=7, isolated=(0, 17, 499), hubs={3: 200}, self_loops=5,
+                              duplicates=6),
+             undirected_graph(rng, 300, 3, components=1, shuffle_rows=True),
+             random_csr(rng, 400, 400, 5)[:2],      # not symmetric: the sequential search does not care
+             (np.zeros(6, np.int32), np.zeros(0, np.int32))]
+    for rp, ci in cases:
+        n = rp.size - 1
+        p = oracle.bfs_order(rp, ci)
+        assert np.array_equal(np.sort(p), np.arange(n))
+        got, want = oracle.permutate_csr(rp, ci, p), oracle.ref_bfs_graph(rp, ci)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        q = oracle.degree_order(rp)
+        assert np.array_equal(np.sort(q), np.arange(n))
+        got, want = oracle.permutate_csr(rp, ci, q), oracle.ref_max_degree_sort_graph(rp, ci)
+        assert np.array_equal(got[0], want[0])
+    # all degrees distinct: vertex i lists i of the other vertices
+    n = 120
+    perm = rng.permutation(n)
+    rows = [np.sort(rng.choice(n, size=d, replace=False)) for d in perm]
+    rp = np.zeros(n + 1, np.int32)
+    rp[1:] = np.cumsum(perm)
+    ci = np.concatenate(rows).astype(np.int32)
+    got, want = oracle.permutate_csr(rp, ci, oracle.degree_order(rp)), oracle.ref_max_degree_sort_graph(rp, ci)
+    assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
