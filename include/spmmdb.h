@@ -270,8 +270,8 @@ int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* coli
                                 int64_t* dist10_host, void* stream);
 
 /* --------------------------------------------------------------------------
- * The reference's two simple orderings produced on the device.  Both write the permutation
- * old2new[n] (DEVICE) that spmmdb_permute_csr_f32 / spmmdb_permute_rows_f32 apply; both synchronise `stream`.
+ * The reference's simple orderings produced on the device.  Each writes the permutation
+ * old2new[n] (DEVICE) that spmmdb_permute_csr_f32 / spmmdb_permute_rows_f32 apply, and synchronises `stream`.
  *   spmmdb_order_by_degree  maxDegreeSort (reorder_strategy.cc:41-55): descending degree.  The reference leaves
  *                           equal degrees in whatever order std::sort gives; here ties keep ascending id, so the
  *                           permuted graph has the reference's row lengths always, its rows when degrees differ.
@@ -285,6 +285,11 @@ int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* coli
  * ------------------------------------------------------------------------ */
 int spmmdb_order_by_degree(int n, const int* rowptr, int* old2new, void* stream);
 int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int* old2new, void* stream);
+/* reverseCuthillMcKee (reorder_strategy.cc:57-66): adjacency lists sorted by descending degree of the neighbour, then
+ * BFSTraversal (the reference never reverses the order).  Equal-degree neighbours are taken in ascending id; the
+ * reference's std::sort leaves them unspecified (stable for lists of <= 16 entries: on graphs of maximum degree <= 16
+ * this is the reference's permutation exactly). */
+int spmmdb_order_rcm(int n, const int* rowptr, const int* colind, int* old2new, void* stream);
 
 /* --------------------------------------------------------------------------
  * Host-buffer variant of spmmdb_csrmm_f32 (row-major B and C, ld = K): all

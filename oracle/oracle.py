@@ -189,6 +189,18 @@ def bfs_order(rowptr, colind):
     return out[:n]
 
 
+def rcm_order(rowptr, colind):
+    """old2new of reverseCuthillMcKee (reorder_strategy.cc:57-66): every list sorted by descending degree of the
+    neighbour (ties keep list order, i.e. a stable sort; the reference's std::sort is stable only for lists of at
+    most 16 entries), then BFSTraversal."""
+    rowptr, colind = _i32(rowptr), _i32(colind)
+    n = rowptr.size - 1
+    deg = np.diff(rowptr)
+    rows = np.repeat(np.arange(n), deg)
+    order = np.lexsort((np.arange(colind.size), -deg[colind].astype(np.int64), rows))
+    return bfs_order(rowptr, colind[order])
+
+
 def degree_order(rowptr):
     """old2new of maxDegreeSort (reorder_strategy.cc:41-55), equal degrees in ascending id."""
     rowptr = _i32(rowptr)

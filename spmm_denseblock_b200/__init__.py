@@ -11,7 +11,7 @@ from ._lib import lib, lib_path, SpmmdbError  # noqa: F401
 from .ops import (  # noqa: F401
     ROW_MAJOR, COL_MAJOR, DIR_ROW, DIR_COLUMN, MATH_FP32, MATH_TF32, MATH_BF16, MATH_BF16_PACKED, bsr_pack_bf16,
     gespmm_csrmm, csrmm, bsrmm, rocsparse_bsrmm, block_gemm, bsr_transpose_blocks, csr2bsr_nnz, csr2bsr, bsr2csr,
-    csrmm_segment, set_csrmm_segment, set_tuning, get_tuning, csrmm_ex, csrmm_noalloc, csr_hot_columns, dense_pack_bf16, divide, divide_threshold, permute_csr, permute_rows, order_by_degree, order_bfs, heatmap, block_metrics, block_fill_histogram, Hybrid,
+    csrmm_segment, set_csrmm_segment, set_tuning, get_tuning, csrmm_ex, csrmm_noalloc, csr_hot_columns, dense_pack_bf16, divide, divide_threshold, permute_csr, permute_rows, order_by_degree, order_bfs, order_rcm, heatmap, block_metrics, block_fill_histogram, Hybrid,
 )
 from .graphio import (  # noqa: F401
     GRAPH_TEXT, GRAPH_BINARY, GRAPH_EDGELIST, GRAPH_AUTO, read_graph, write_graph,

@@ -25,6 +25,7 @@ SIGNATURES = {
     "spmmdb_csrmm_noalloc_f32": [C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, c_i64, vp, c_i64, C.c_float, C.c_float, vp],
     "spmmdb_order_by_degree": [C.c_int, vp, vp, vp],
     "spmmdb_order_bfs": [C.c_int, vp, vp, vp, vp],
+    "spmmdb_order_rcm": [C.c_int, vp, vp, vp, vp],
     "spmmdb_csr_hot_columns": [C.c_int, c_i64, vp, c_i64, vp, C.POINTER(C.c_int), vp],
     "spmmdb_dense_pack_bf16": [c_i64, C.c_int, vp, c_i64, vp, c_i64, vp],
     "spmmdb_csrmm_segment": [c_i64],

@@ -28,11 +28,11 @@ __global__ void __launch_bounds__(256) perm_degree_kernel(int n, const int* __re
                                                           int* __restrict__ counters, int* __restrict__ list4,
                                                           int* __restrict__ list16, int* __restrict__ list_s,
                                                           int* __restrict__ list_m, int* __restrict__ list_l,
-                                                          int* __restrict__ list_h) {
+                                                          int* __restrict__ list_h, int rows_stay) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int d = __ldg(rowptr + i + 1) - __ldg(rowptr + i);
-  new_deg[__ldg(old2new + i)] = d;
+  if (!rows_stay) new_deg[__ldg(old2new + i)] = d;
   if (d > kLargeRow) list_h[atomicAdd(counters + 5, 1)] = i;
   else if (d > kMediumRow) list_l[atomicAdd(counters + 4, 1)] = i;
   else if (d > kSmallCtaRow) list_m[atomicAdd(counters + 3, 1)] = i;
@@ -109,7 +109,6 @@ struct BitonicSort<E, K, 0> {
   static __device__ __forceinline__ void run(K (&)[E], int, unsigned) {}
 };
 template <int E> struct Log2Keys;
-template <> struct Log2Keys<1> { static constexpr int v = 5; };
 template <> struct Log2Keys<4> { static constexpr int v = 7; };
 template <> struct Log2Keys<16> { static constexpr int v = 9; };
 
@@ -119,7 +118,7 @@ __global__ void __launch_bounds__(128) perm_warp_kernel(int n, const int* __rest
                                                         const int* __restrict__ rowptr, const int* __restrict__ colind,
                                                         const float* __restrict__ val, const int* __restrict__ old2new,
                                                         const int* __restrict__ new_rowptr, int* __restrict__ new_colind,
-                                                        float* __restrict__ new_val, int pbits) {
+                                                        float* __restrict__ new_val, int pbits, int rows_stay) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -136,7 +135,7 @@ __global__ void __launch_bounds__(128) perm_warp_kernel(int n, const int* __rest
       if (t < d) key[e] = ((K)(unsigned)__ldg(old2new + __ldg(colind + s + t)) << pbits) | (K)(unsigned)t;
     }
     BitonicSort<E, K, Log2Keys<E>::v>::run(key, lane, 0u);
-    const int64_t o = __ldg(new_rowptr + __ldg(old2new + i));
+    const int64_t o = __ldg(new_rowptr + (rows_stay ? i : __ldg(old2new + i)));
 #pragma unroll
     for (int e = 0; e < E; ++e) {
       const int t = (e << 5) | lane;
@@ -154,7 +153,7 @@ template <typename K, int R>
 __global__ void __launch_bounds__(128) perm_warp1_kernel(int n, const int* __restrict__ rowptr, const int* __restrict__ colind,
                                                          const float* __restrict__ val, const int* __restrict__ old2new,
                                                          const int* __restrict__ new_rowptr, int* __restrict__ new_colind,
-                                                         float* __restrict__ new_val, int pbits) {
+                                                         float* __restrict__ new_val, int pbits, int rows_stay) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -177,7 +176,7 @@ __global__ void __launch_bounds__(128) perm_warp1_kernel(int n, const int* __res
     for (int u = 0; u < R; ++u) {
       key[u][0] = ~(K)0;
       if (lane < d[u]) key[u][0] = ((K)(unsigned)__ldg(old2new + __ldg(colind + s[u] + lane)) << pbits) | (K)(unsigned)lane;
-      if (d[u] > 0) o[u] = __ldg(new_rowptr + __ldg(old2new + r0 + u));
+      if (d[u] > 0) o[u] = __ldg(new_rowptr + (rows_stay ? (int)(r0 + u) : __ldg(old2new + r0 + u)));
     }
 #pragma unroll
     for (int u = 0; u < R; ++u) BitonicSort<1, K, 5>::run(key[u], lane, 0u);
@@ -200,7 +199,8 @@ __global__ void __launch_bounds__(512) perm_cta_kernel(const int* __restrict__ l
                                                        const int* __restrict__ colind, const float* __restrict__ val,
                                                        const int* __restrict__ old2new,
                                                        const int* __restrict__ new_rowptr, int* __restrict__ new_colind,
-                                                       float* __restrict__ new_val, unsigned long long* gstage) {
+                                                       float* __restrict__ new_val, unsigned long long* gstage,
+                                                       int rows_stay) {
   typedef unsigned long long K;
   constexpr int E = 16, kChunk = 32 * E;
   extern __shared__ unsigned long long skeys[];
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(512) perm_cta_kernel(const int* __restrict__ l
       }
       __syncthreads();
     }
-    const int64_t o = __ldg(new_rowptr + __ldg(old2new + i));
+    const int64_t o = __ldg(new_rowptr + (rows_stay ? i : __ldg(old2new + i)));
     for (int t = threadIdx.x; t < d; t += blockDim.x) {
       const K k = keys[t];
       new_colind[o + t] = (int)(k >> 32);
@@ -293,18 +293,13 @@ int exclusive_scan_i32(const int* counts, int n, int* sums, int* out, cudaStream
 
 }  // namespace spmmdb
 
-using namespace spmmdb;
-
-extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colind, const float* val,
-                                      const int* old2new, int* new_rowptr, int* new_colind, float* new_val,
-                                      void* stream) {
-  if (n < 0) return SPMMDB_ERR_INVALID_VALUE;
-  if (new_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
-  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (n == 0) { SPMMDB_CUDA_OK(cudaMemsetAsync(new_rowptr, 0, sizeof(int), st)); return SPMMDB_OK; }
-  if (rowptr == nullptr || old2new == nullptr) return SPMMDB_ERR_INVALID_VALUE;
-  if (val != nullptr && new_val == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+namespace spmmdb {
+// The relabel-and-sort pass behind spmmdb_permute_csr_f32.  rows_stay == 0: A' = P A P^T (rows move to old2new[i],
+// new_rowptr is written).  rows_stay == 1: rows keep their place (new_rowptr must be rowptr) and only the columns are
+// relabelled and sorted -- new_colind[t] = old2new[column], ascending within the row: every adjacency list ordered
+// by a per-vertex key (spmmdb_order_rcm: the key is the degree rank).
+int permute_csr_impl(int n, const int* rowptr, const int* colind, const float* val, const int* old2new, int rows_stay,
+                     int* new_rowptr, int* new_colind, float* new_val, cudaStream_t st) {
   // scratch: counters[8] | new_deg[n] | scan sums | six row lists of n entries
   const int ntiles = (n + 2047) / 2048 + 1;
   const size_t ints = 8 + (size_t)n + ntiles + 8 + 6 * (size_t)n;
@@ -321,10 +316,12 @@ extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colin
   int* list_h = list_l + n;
   SPMMDB_CUDA_OK(cudaMemsetAsync(counters, 0, 8 * sizeof(int), st));
   perm_degree_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, rowptr, old2new, new_deg, counters, list4, list16, list_s, list_m,
-                                                      list_l, list_h);
+                                                      list_l, list_h, rows_stay);
   SPMMDB_CUDA_OK(cudaGetLastError());
-  int rc = exclusive_scan_i32(new_deg, n, sums, new_rowptr, st);
-  if (rc != SPMMDB_OK) return rc;
+  if (!rows_stay) {
+    int rc = exclusive_scan_i32(new_deg, n, sums, new_rowptr, st);
+    if (rc != SPMMDB_OK) return rc;
+  }
   int h[6] = {0, 0, 0, 0, 0, 0};
   SPMMDB_CUDA_OK(cudaMemcpyAsync(h, counters, sizeof(h), cudaMemcpyDeviceToHost, st));
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
@@ -337,20 +334,22 @@ extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colin
   do {                                                                                                             \
     if (narrow(PBITS))                                                                                             \
       perm_warp_kernel<E, unsigned><<<warp_grid(ROWS), 128, 0, st>>>(n, LIST, COUNT, rowptr, colind, val, old2new, \
-                                                                     new_rowptr, new_colind, new_val, PBITS);      \
+                                                                     new_rowptr, new_colind, new_val, PBITS,       \
+                                                                     rows_stay);                                   \
     else                                                                                                           \
       perm_warp_kernel<E, unsigned long long><<<warp_grid(ROWS), 128, 0, st>>>(                                    \
-          n, LIST, COUNT, rowptr, colind, val, old2new, new_rowptr, new_colind, new_val, 32);                      \
+          n, LIST, COUNT, rowptr, colind, val, old2new, new_rowptr, new_colind, new_val, 32, rows_stay);           \
     SPMMDB_CUDA_OK(cudaGetLastError());                                                                            \
   } while (0)
   {
     const int64_t want = ((int64_t)n + 15) / 16;  // 4 warps x 4 rows per CTA and iteration
     const int grid = (int)(want < (int64_t)nsm * 16 ? want : (int64_t)nsm * 16);
     if (narrow(5))
-      perm_warp1_kernel<unsigned, 4><<<grid, 128, 0, st>>>(n, rowptr, colind, val, old2new, new_rowptr, new_colind, new_val, 5);
+      perm_warp1_kernel<unsigned, 4><<<grid, 128, 0, st>>>(n, rowptr, colind, val, old2new, new_rowptr, new_colind, new_val, 5,
+                                                           rows_stay);
     else
       perm_warp1_kernel<unsigned long long, 4><<<grid, 128, 0, st>>>(n, rowptr, colind, val, old2new, new_rowptr, new_colind,
-                                                                     new_val, 32);
+                                                                     new_val, 32, rows_stay);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
   if (h[0] > 0) SPMMDB_PERM_WARP(4, 7, list4, counters + 0, h[0]);
@@ -359,20 +358,20 @@ extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colin
   if (h[2] > 0) {
     const int grid = h[2] < nsm * 12 ? h[2] : nsm * 12;
     perm_cta_kernel<<<grid, 64, kSmallCtaRow * 8, st>>>(list_s, counters + 2, kSmallCtaRow, rowptr, colind, val, old2new,
-                                                       new_rowptr, new_colind, new_val, nullptr);
+                                                       new_rowptr, new_colind, new_val, nullptr, rows_stay);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
   if (h[3] > 0) {
     const int grid = h[3] < nsm * 3 ? h[3] : nsm * 3;
     perm_cta_kernel<<<grid, 256, kMediumRow * 8, st>>>(list_m, counters + 3, kMediumRow, rowptr, colind, val, old2new,
-                                                       new_rowptr, new_colind, new_val, nullptr);
+                                                       new_rowptr, new_colind, new_val, nullptr, rows_stay);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
   if (h[4] > 0) {
     SPMMDB_CUDA_OK(cudaFuncSetAttribute(perm_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kLargeRow * 8));
     const int grid = h[4] < nsm ? h[4] : nsm;
     perm_cta_kernel<<<grid, 512, kLargeRow * 8, st>>>(list_l, counters + 4, kLargeRow, rowptr, colind, val, old2new,
-                                                     new_rowptr, new_colind, new_val, nullptr);
+                                                     new_rowptr, new_colind, new_val, nullptr, rows_stay);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
   if (h[5] > 0) {
@@ -384,10 +383,26 @@ extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colin
     if (stage == nullptr) return SPMMDB_ERR_ALLOC;
     const int grid = h[5] < nsm * 2 ? h[5] : nsm * 2;
     perm_cta_kernel<<<grid, 512, 0, st>>>(list_h, counters + 5, 0, rowptr, colind, val, old2new, new_rowptr, new_colind,
-                                          new_val, stage);
+                                          new_val, stage, rows_stay);
     SPMMDB_CUDA_OK(cudaGetLastError());
   }
   return SPMMDB_OK;
+}
+}  // namespace spmmdb
+
+using namespace spmmdb;
+
+extern "C" int spmmdb_permute_csr_f32(int n, const int* rowptr, const int* colind, const float* val,
+                                      const int* old2new, int* new_rowptr, int* new_colind, float* new_val,
+                                      void* stream) {
+  if (n < 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (new_rowptr == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) { SPMMDB_CUDA_OK(cudaMemsetAsync(new_rowptr, 0, sizeof(int), st)); return SPMMDB_OK; }
+  if (rowptr == nullptr || old2new == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (val != nullptr && new_val == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  return permute_csr_impl(n, rowptr, colind, val, old2new, 0, new_rowptr, new_colind, new_val, st);
 }
 
 extern "C" int spmmdb_permute_rows_f32(int rows, int K, const float* in, int64_t ldi, const int* old2new, float* out,

@@ -1,4 +1,4 @@
-// reorder.cu -- the two simple orderings of the reference produced on the device: the permutation
+// reorder.cu -- the simple orderings of the reference produced on the device: the permutation
 // old2new only; applying it is spmmdb_permute_csr_f32 / spmmdb_permute_rows_f32 (permute.cu).
 //
 //   spmmdb_order_by_degree   maxDegreeSort (reorder_strategy.cc:41-55): vertices by descending degree.  The reference
@@ -27,6 +27,8 @@
 
 namespace spmmdb {
 int exclusive_scan_i32(const int* counts, int n, int* sums, int* out, cudaStream_t st);  // convert.cu
+int permute_csr_impl(int n, const int* rowptr, const int* colind, const float* val, const int* old2new, int rows_stay,
+                     int* new_rowptr, int* new_colind, float* new_val, cudaStream_t st);  // permute.cu
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
@@ -196,6 +198,11 @@ __global__ void __launch_bounds__(256) bfs_number_kernel(int nf, const int* __re
   }
 }
 
+__global__ void __launch_bounds__(256) map_kernel(int64_t cnt, const int* __restrict__ table, int* __restrict__ x) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += stride) x[i] = __ldg(table + x[i]);
+}
+
 inline int blocks_for(int64_t n, int per = 256) { return (int)((n + per - 1) / per); }
 
 }  // namespace
@@ -325,4 +332,39 @@ extern "C" int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int
     return SPMMDB_ERR_NOT_SUPPORTED;
   }
   return SPMMDB_OK;
+}
+
+// reverseCuthillMcKee (reorder_strategy.cc:57-66): every adjacency list sorted by descending degree of the neighbour,
+// then BFSTraversal.  (Despite the name the reference never reverses the order.)  Sorting a list by descending degree
+// with ties in ascending id is sorting it by the neighbours' rank in spmmdb_order_by_degree, which the relabel-and-
+// sort pass of permute.cu does with the rows left in place.  The reference sorts with std::sort, which leaves equal
+// degrees in an unspecified order: lists of at most 16 entries come out stable there (insertion sort), so on graphs of
+// maximum degree <= 16 this is the reference's permutation exactly; beyond that it is the same search with the ties
+// among equal-degree neighbours taken in ascending id.
+extern "C" int spmmdb_order_rcm(int n, const int* rowptr, const int* colind, int* old2new, void* stream) {
+  if (n < 0) return SPMMDB_ERR_INVALID_VALUE;
+  if (n == 0) return SPMMDB_OK;
+  if (rowptr == nullptr || old2new == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  if (device_sm() < 0) return SPMMDB_ERR_CUDA;
+  cudaStream_t st = (cudaStream_t)stream;
+  int nnz = 0;
+  SPMMDB_CUDA_OK(cudaMemcpyAsync(&nnz, rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
+  if (nnz > 0 && colind == nullptr) return SPMMDB_ERR_INVALID_VALUE;
+  int* tmp = (int*)scratch(kScratchLayoutC, sizeof(int) * (2 * (size_t)n + (size_t)nnz + 8), st);
+  if (tmp == nullptr) return SPMMDB_ERR_ALLOC;
+  int* rank = tmp;           // rank[v]: position of v by (descending degree, ascending id)
+  int* by_rank = tmp + n;    // its inverse
+  int* lists = by_rank + n;  // the adjacency lists, each sorted by rank
+  int rc = spmmdb_order_by_degree(n, rowptr, rank, stream);
+  if (rc != SPMMDB_OK) return rc;
+  invert_kernel<<<blocks_for(n), 256, 0, st>>>(n, rank, by_rank);
+  if (nnz > 0) {
+    rc = permute_csr_impl(n, rowptr, colind, nullptr, rank, /*rows_stay=*/1, const_cast<int*>(rowptr), lists, nullptr, st);
+    if (rc != SPMMDB_OK) return rc;
+    const int nsm = device_num_sms() > 0 ? device_num_sms() : 148;
+    map_kernel<<<nsm * 8, 256, 0, st>>>(nnz, by_rank, lists);
+  }
+  SPMMDB_CUDA_OK(cudaGetLastError());
+  return spmmdb_order_bfs(n, rowptr, lists, old2new, stream);
 }

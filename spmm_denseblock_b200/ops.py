@@ -286,6 +286,15 @@ def order_bfs(rowptr, colind):
     return old2new
 
 
+def order_rcm(rowptr, colind):
+    """old2new of reverseCuthillMcKee (reorder_strategy.cc:57-66): lists by descending degree (ties: ascending id), BFS."""
+    _dev(rowptr, colind)
+    n = rowptr.numel() - 1
+    old2new = torch.empty(n, dtype=torch.int32, device=rowptr.device)
+    check(lib().spmmdb_order_rcm(n, _p(rowptr), _p(colind), _p(old2new), _stream()), "spmmdb_order_rcm")
+    return old2new
+
+
 def permute_rows(X, old2new):
     """out[old2new[r]] = X[r] for a row-major dense matrix."""
     _dev(X, old2new)

@@ -718,6 +718,26 @@ def test_order_bfs_config_shapes_and_refusal(pkg, oracle):
     assert rc == -2 and b"not symmetric" in pkg.lib().spmmdb_last_error()
 
 
+def test_order_rcm(pkg, oracle):
+    """spmmdb_order_rcm == reverseCuthillMcKee (reorder_strategy.cc:57-66) with equal-degree neighbours in ascending
+    id: the restatement's permutation on graphs with hubs and unsorted lists; the reference's own output graph where
+    its std::sort is stable (maximum degree <= 16)."""
+    from helpers import undirected_graph
+    rng = np.random.default_rng(31)
+    big = undirected_graph(rng, 6000, 6, components=3, isolated=(1, 2), hubs={4: 700, 90: 5000, 91: 40}, self_loops=10)
+    low = undirected_graph(rng, 5000, 3, components=6, isolated=(0,))
+    assert np.diff(low[0]).max() <= 16
+    for rp, ci in (big, low, (np.zeros(4, np.int32), np.zeros(0, np.int32))):
+        # ascending lists: the restatement's stable sort then breaks degree ties by ascending id, like the device
+        p = pkg.order_rcm(dev(rp), dev(ci))
+        assert np.array_equal(p.cpu().numpy(), oracle.rcm_order(rp, ci))
+    rp, ci = low
+    p = pkg.order_rcm(dev(rp), dev(ci))
+    nrp, nci, _ = pkg.permute_csr(dev(rp), dev(ci), None, p)
+    wrp, wci = oracle.ref_rcmk_graph(rp, ci)
+    assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
+
+
 def test_order_by_degree(pkg, oracle):
     """spmmdb_order_by_degree == maxDegreeSort (reorder_strategy.cc:41-55) with ties in ascending id: the
     restatement's permutation exactly; the reference's row lengths always, its rows when all degrees differ."""

@@ -229,3 +229,19 @@ def test_bfs_and_degree_order_restatements_match_the_reference(oracle):
     ci = np.concatenate(rows).astype(np.int32)
     got, want = oracle.permutate_csr(rp, ci, oracle.degree_order(rp)), oracle.ref_max_degree_sort_graph(rp, ci)
     assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+def test_rcm_order_restatement_matches_the_reference_where_std_sort_is_stable(oracle):
+    """reverseCuthillMcKee (reorder_strategy.cc:57-66) sorts every list by degree with std::sort, which is an insertion
+    sort (stable) for lists of at most 16 entries: on graphs of maximum degree <= 16 the restatement (stable sort +
+    BFSTraversal) reproduces the reference's output graph bit for bit."""
+    if oracle.ref_host_lib() is None:
+        pytest.skip("oracle/_ref/libref_host.so not built")
+    from helpers import undirected_graph
+    rng = np.random.default_rng(12)
+    for n, avg, comps in ((4000, 3, 5), (1500, 2.2, 40), (600, 4, 1)):
+        rp, ci = undirected_graph(rng, n, avg, components=comps, isolated=(5,), shuffle_rows=True)
+        assert np.diff(rp).max() <= 16
+        p = oracle.rcm_order(rp, ci)
+        got, want = oracle.permutate_csr(rp, ci, p), oracle.ref_rcmk_graph(rp, ci)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
