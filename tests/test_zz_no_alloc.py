@@ -120,4 +120,4 @@ def test_noalloc_rejects_sizes_beyond_the_limit_and_allocates_nothing(pkg):
     for K in (32, 256, 512):
         assert call_noalloc(pkg, rp, ci, v, B, MAX_K + 4, Cm, MAX_K + 4, m, k, K, 1.0, 0.0) == 0
     torch.cuda.synchronize()
-    assert torch.cuda.mem_get_info()[0] == free0
+    assert torch.cuda.mem_get_info()[0] >= free0 - (1 << 20)  # a cudaMalloc would take at least 2 MB
