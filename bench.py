@@ -9,7 +9,8 @@ configs[4]: the ogbn-products-shaped power-law graph (2,449,029 nodes, 61,859,14
 preferentially, K = 256, fp32, CSR), sharded by nnz-balanced row ranges over the N GPUs.  The other configs run with
 --workload / --op (one GPU):
 
-    --workload c1_uniform | c2_arxiv | c3_proteins | c3_proteins_shuffled | c3_proteins_rcm | c3_proteins_gorder |
+    --workload c1_uniform | c2_arxiv | c3_proteins | c3_proteins_shuffled | c3_proteins_rcm | c3_proteins_rcm_gpu |
+               c3_proteins_gorder |
                c4_molhiv | c5_products | c5_products_local
     --op       csr | csr_bf16b | bsr16 | bsr32 | hybrid16 | hybrid32 | block_gemm16 | block_gemm32   [--math tf32|bf16|fp32]
 
@@ -37,6 +38,9 @@ WORKLOADS = {
     "c3_proteins_rcm": ("c3_proteins", dict(shuffle=True), 128,
                         "configs[2] shuffled, then reordered by the reference's reverseCuthillMcKee "
                         "(reorder_strategy.cc:57-98; permutation from tests/golden/c3_orders.npz)"),
+    "c3_proteins_rcm_gpu": ("c3_proteins", dict(shuffle=True), 128,
+                            "configs[2] shuffled, then reordered ON THE DEVICE by spmmdb_order_rcm (the reference's "
+                            "reverseCuthillMcKee, reorder_strategy.cc:57-98, with equal-degree neighbours in ascending id)"),
     "c3_proteins_gorder": ("c3_proteins", dict(shuffle=True), 128,
                            "configs[2] shuffled, then reordered by the reference's vendored Gorder (Gorder/main.cpp, "
                            "window 5; permutation from tests/golden/c3_orders.npz)"),
@@ -198,7 +202,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     cfg_name, overrides, K, desc = WORKLOADS[a.workload]
-    reordered = a.workload in ("c3_proteins_rcm", "c3_proteins_gorder")
+    reordered = a.workload in ("c3_proteins_rcm", "c3_proteins_gorder", "c3_proteins_rcm_gpu")
     cpu_graph = "shuffle" in overrides  # the permutation fixtures belong to the CPU generator's graph
     big = a.workload.startswith(("c5", "c4"))
     config = {"workload": f"{a.workload}: {desc}; op {a.op}", "K": K, "op": a.op,
@@ -264,11 +268,18 @@ def main():
     # ---- config 3 as BASELINE.json states it: CPU reorderer -> permutation -> (csr2bsr ->) SpMM -------------------
     unperm = None
     if reordered:
-        fx = np.load(os.path.join(ROOT, "tests", "golden", "c3_orders.npz"))
-        fp = np.array([n, nnz, int(rp.cpu().numpy()[::997].astype(np.int64).sum() % (1 << 31)),
-                       int((ci.cpu().numpy()[::9973].astype(np.int64) * 31 % 1000003).sum() % (1 << 31))], np.int64)
-        assert a.scale == 1.0 and np.array_equal(fp, fx["fingerprint"]), "c3_orders.npz belongs to another graph"
-        old2new = torch.from_numpy(fx["old2new_" + a.workload.rsplit("_", 1)[1]].astype(np.int32)).to(dev)
+        if a.workload.endswith("_gpu"):
+            pkg.order_rcm(rp, ci)  # warm-up (scratch, kernels)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            old2new = pkg.order_rcm(rp, ci)  # C ABI: spmmdb_order_rcm (synchronises)
+            extra["order_rcm_ms_once"] = (time.perf_counter() - t0) * 1e3
+        else:
+            fx = np.load(os.path.join(ROOT, "tests", "golden", "c3_orders.npz"))
+            fp = np.array([n, nnz, int(rp.cpu().numpy()[::997].astype(np.int64).sum() % (1 << 31)),
+                           int((ci.cpu().numpy()[::9973].astype(np.int64) * 31 % 1000003).sum() % (1 << 31))], np.int64)
+            assert a.scale == 1.0 and np.array_equal(fp, fx["fingerprint"]), "c3_orders.npz belongs to another graph"
+            old2new = torch.from_numpy(fx["old2new_" + a.workload.rsplit("_", 1)[1]].astype(np.int32)).to(dev)
         rp0, ci0, B0 = rp, ci, B
         t0 = time.perf_counter()
         rp, ci, val = pkg.permute_csr(rp0, ci0, val, old2new)   # A' = P A P^T on the device

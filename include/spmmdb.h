@@ -276,11 +276,8 @@ int spmmdb_block_fill_histogram(int m, int n, const int* rowptr, const int* coli
  *                           equal degrees in whatever order std::sort gives; here ties keep ascending id, so the
  *                           permuted graph has the reference's row lengths always, its rows when degrees differ.
  *   spmmdb_order_bfs        BFSTraversal (reorder_strategy.cc:68-98): FIFO breadth-first numbering, started at the
- *                           lowest unvisited id, neighbours in adjacency order (colind need not be sorted; feed
- *                           lists sorted by descending degree for reverseCuthillMcKee, :57-66).  The reference's
- *                           permutation exactly, for a symmetric pattern (undirected graph); a pattern where the
- *                           search from a component's lowest id does not reach the whole weakly connected
- *                           component returns SPMMDB_ERR_NOT_SUPPORTED.
+ *                           lowest unvisited id, neighbours in adjacency order (colind need not be sorted).  The
+ *                           reference's permutation exactly, for any pattern, symmetric or not.
  * The other front-ends (Gorder, Rabbit, METIS, greedy) stay on the CPU (BASELINE.json north_star).
  * ------------------------------------------------------------------------ */
 int spmmdb_order_by_degree(int n, const int* rowptr, int* old2new, void* stream);

@@ -7,20 +7,22 @@
 //                            rows whenever the degrees are distinct.
 //   spmmdb_order_bfs         BFSTraversal (reorder_strategy.cc:68-98): the numbering a FIFO breadth-first search gives,
 //                            started at the lowest unvisited id, neighbours taken in adjacency order.  Exactly the
-//                            reference's permutation for a symmetric pattern (an undirected graph, what the
-//                            reference's datasets are); a pattern whose search from the lowest id of a weakly
-//                            connected component does not reach all of it is refused (SPMMDB_ERR_NOT_SUPPORTED).
-//                            reverseCuthillMcKee (:57-66) is this search on adjacency lists sorted by descending
-//                            degree.
+//                            reference's permutation, for any pattern (symmetric or not).
+//   spmmdb_order_rcm         reverseCuthillMcKee (:57-66): that search on adjacency lists sorted by descending degree.
 //
-// Integer work, deterministic.  The search runs level by level for ALL components at once: a sequential FIFO search
-// numbers a component completely before the next one starts, components in the order of their lowest id, and inside
-// a component level by level, a level in the order (position of the parent in its level, position in the parent's
-// adjacency list) with the parent being the first frontier vertex that lists the child.  So
-//   old2new[v] = (vertices in components with a lower lowest id) + (vertices of v's component in earlier levels)
-//                + (rank of v in its level among its component's vertices),
+// Integer work, deterministic.  The search runs level by level for ALL roots at once.  A sequential FIFO search
+// restarts at the lowest unvisited id whenever its queue runs empty; vertex v is therefore numbered by the search of
+// root label(v) = the lowest id among the vertices that can reach v (if a smaller vertex reached v, that vertex or its
+// own root would have claimed v first), the roots are the vertices with label(v) = v, and the search of root r visits
+// exactly T_r = { v : label(v) = r }: an edge out of T_r leads into T_r or into the territory of a smaller root, which
+// is already numbered, and every vertex of T_r is reached from r through T_r alone.  (For a symmetric pattern T_r is a
+// connected component and r its lowest id.)  Inside T_r the search numbers level by level, a level in the order
+// (position of the parent in its level, position in the parent's adjacency list), the parent being the first frontier
+// vertex that lists the child.  So
+//   old2new[v] = (vertices with a smaller label) + (vertices of T_label(v) in earlier levels)
+//                + (rank of v in its level among the vertices with its label),
 // and the frontier array of a level, built by stable compaction of the winning (parent, position) slots, is ordered
-// by component first because the roots are.
+// by label first because the roots are.
 #include <limits.h>
 
 #include "common.cuh"
@@ -77,9 +79,10 @@ __global__ void __launch_bounds__(256) iota_fill_kernel(int n, int* __restrict__
   if (i < n) { label[i] = i; key[i] = key_init; }
 }
 
-// Connected components as "lowest id of the component": labels only ever decrease and only take ids of the same
-// component, so the fixed point (every edge joins equal labels, every label is its own label) is that lowest id.
-// A warp per row; hooks the smaller label onto both endpoints and onto their current labels.
+// label[v] = lowest id among the vertices that reach v (v included): the root whose search numbers v.  An edge u -> v
+// hands u's label to v; labels only decrease and label[label[v]] reaches v too, so jumping to it is valid.  The fixed
+// point is reached when no edge and no jump lowers anything.  (On a symmetric pattern these are the connected
+// components, labelled by their lowest id.)  A warp per row.
 __global__ void __launch_bounds__(256) cc_hook_kernel(int n, const int* __restrict__ rowptr, const int* __restrict__ colind,
                                                       int* label, int* __restrict__ changed) {
   const int lane = threadIdx.x & 31;
@@ -88,18 +91,11 @@ __global__ void __launch_bounds__(256) cc_hook_kernel(int n, const int* __restri
   bool any = false;
   for (int64_t u = warp; u < n; u += nwarps) {
     const int s = __ldg(rowptr + u), e = __ldg(rowptr + u + 1);
-    int lu = __ldcg(label + u);
+    const int lu = __ldcg(label + u);
     for (int p = s + lane; p < e; p += 32) {
       const int v = __ldg(colind + p);
-      const int lv = __ldcg(label + v);
-      if (lv < lu) {
-        atomicMin(label + u, lv);
-        atomicMin(label + lu, lv);
-        lu = lv;
-        any = true;
-      } else if (lu < lv) {
+      if (lu < __ldcg(label + v)) {
         atomicMin(label + v, lu);
-        atomicMin(label + lv, lu);
         any = true;
       }
     }
@@ -107,16 +103,17 @@ __global__ void __launch_bounds__(256) cc_hook_kernel(int n, const int* __restri
   if (__any_sync(FULL, any) && lane == 0) *changed = 1;
 }
 
-__global__ void __launch_bounds__(256) cc_jump_kernel(int n, int* label) {
+__global__ void __launch_bounds__(256) cc_jump_kernel(int n, int* label, int* __restrict__ changed) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n) return;
-  int l = __ldcg(label + v);
+  const int l0 = __ldcg(label + v);
+  int l = l0;
   for (;;) {
     const int ll = __ldcg(label + l);
     if (ll == l) break;
     l = ll;
   }
-  label[v] = l;
+  if (l < l0) { atomicMin(label + v, l); *changed = 1; }
 }
 
 // out[i] = 1 where vertex i is the lowest id of its component; size[label] counts the component
@@ -153,21 +150,23 @@ __global__ void __launch_bounds__(256) bfs_degree_kernel(int nf, const int* __re
 template <int MODE>
 __global__ void __launch_bounds__(256) bfs_expand_kernel(int nf, const int* __restrict__ frontier, const int* __restrict__ rowptr,
                                                          const int* __restrict__ colind, const int* __restrict__ eoff,
-                                                         const int* old2new, int* key, int* __restrict__ cnt,
-                                                         const int* __restrict__ woff, int* __restrict__ next) {
+                                                         const int* __restrict__ label, const int* old2new, int* key,
+                                                         int* __restrict__ cnt, const int* __restrict__ woff,
+                                                         int* __restrict__ next) {
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t i = warp; i < nf; i += nwarps) {
     const int u = frontier[i];
     const int s = __ldg(rowptr + u), d = __ldg(rowptr + u + 1) - s;
-    const int slot0 = eoff[i];
+    const int slot0 = eoff[i], lu = label[u];
     int run = 0;
     for (int j0 = 0; j0 < d; j0 += 32) {
       const int j = j0 + lane;
       int v = -1;
       bool open = false;
-      if (j < d) { v = __ldg(colind + s + j); open = __ldcg(old2new + v) < 0; }
+      // a neighbour with another label belongs to an earlier root's search (numbered before this one started)
+      if (j < d) { v = __ldg(colind + s + j); open = __ldcg(old2new + v) < 0 && label[v] == lu; }
       if (MODE == 0) {
         if (open) atomicMin(key + v, slot0 + j);
       } else {
@@ -277,12 +276,11 @@ extern "C" int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int
   for (int it = 0;; ++it) {
     SPMMDB_CUDA_OK(cudaMemsetAsync(flags, 0, sizeof(int), st));
     cc_hook_kernel<<<wgrid, 256, 0, st>>>(n, rowptr, colind, label, flags);
-    cc_jump_kernel<<<grid, 256, 0, st>>>(n, label);
+    cc_jump_kernel<<<grid, 256, 0, st>>>(n, label, flags);
     int changed = 0;
     SPMMDB_CUDA_OK(cudaMemcpyAsync(&changed, flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
     if (!changed) break;
-    if (it > 4 * 32) return SPMMDB_ERR_CUDA;  // cannot happen: every pass at least halves the label trees
   }
   // 2. roots in id order = level 0; base[c] = vertices in components with a lower lowest id
   SPMMDB_CUDA_OK(cudaMemsetAsync(firsts, 0, sizeof(int) * N, st));
@@ -305,14 +303,14 @@ extern "C" int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int
     bfs_degree_kernel<<<fg, 256, 0, st>>>(nf, fr[cur], rowptr, cnt);
     rc = exclusive_scan_i32(cnt, nf, sums, off, st);
     if (rc != SPMMDB_OK) return rc;
-    bfs_expand_kernel<0><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, old2new, key, nullptr, nullptr, nullptr);
-    bfs_expand_kernel<1><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, old2new, key, cnt, nullptr, nullptr);
+    bfs_expand_kernel<0><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, label, old2new, key, nullptr, nullptr, nullptr);
+    bfs_expand_kernel<1><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, label, old2new, key, cnt, nullptr, nullptr);
     // the counts' scan goes to `firsts` (free between levels); the slot offsets in `off` are still needed
     rc = exclusive_scan_i32(cnt, nf, sums, firsts, st);
     if (rc != SPMMDB_OK) return rc;
     int nn = 0;
     SPMMDB_CUDA_OK(cudaMemcpyAsync(&nn, firsts + nf, sizeof(int), cudaMemcpyDeviceToHost, st));
-    bfs_expand_kernel<2><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, old2new, key, nullptr, firsts, fr[cur ^ 1]);
+    bfs_expand_kernel<2><<<fw, 256, 0, st>>>(nf, fr[cur], rowptr, colind, off, label, old2new, key, nullptr, firsts, fr[cur ^ 1]);
     SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
     if (nn > 0) {
       const int ng = blocks_for(nn);
@@ -326,10 +324,10 @@ extern "C" int spmmdb_order_bfs(int n, const int* rowptr, const int* colind, int
     cur ^= 1;
   }
   SPMMDB_CUDA_OK(cudaStreamSynchronize(st));
-  if (numbered != n) {
-    set_last_error("spmmdb_order_bfs: the pattern is not symmetric (a component is not reached from its lowest id)",
-                   cudaErrorInvalidValue, __FILE__, __LINE__);
-    return SPMMDB_ERR_NOT_SUPPORTED;
+  if (numbered != n) {  // cannot happen with column indices in [0, n): every vertex is reached from its label
+    set_last_error("spmmdb_order_bfs: vertices left unnumbered (column index out of range?)", cudaErrorInvalidValue, __FILE__,
+                   __LINE__);
+    return SPMMDB_ERR_INVALID_VALUE;
   }
   return SPMMDB_OK;
 }

@@ -278,7 +278,7 @@ def order_by_degree(rowptr):
 
 
 def order_bfs(rowptr, colind):
-    """old2new of BFSTraversal (reorder_strategy.cc:68-98) for a symmetric pattern; colind in adjacency order."""
+    """old2new of BFSTraversal (reorder_strategy.cc:68-98); colind in adjacency order (need not be sorted)."""
     _dev(rowptr, colind)
     n = rowptr.numel() - 1
     old2new = torch.empty(n, dtype=torch.int32, device=rowptr.device)

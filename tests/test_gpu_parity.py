@@ -682,8 +682,8 @@ def _order_cases():
 
 @pytest.mark.parametrize("name,graph", list(_order_cases()), ids=lambda x: x if isinstance(x, str) else "")
 def test_order_bfs_is_the_reference_permutation(pkg, oracle, name, graph):
-    """spmmdb_order_bfs == BFSTraversal (reorder_strategy.cc:68-98): the permutation equals the sequential
-    restatement's, and the graph permuted with it on the device equals the reference's own output graph."""
+    """spmmdb_order_bfs == BFSTraversal (reorder_strategy.cc:68-98) on undirected graphs: the permutation equals the
+    sequential restatement's, and the graph permuted with it on the device equals the reference's own output graph."""
     rp, ci = graph
     p = pkg.order_bfs(dev(rp), dev(ci))
     assert np.array_equal(p.cpu().numpy(), oracle.bfs_order(rp, ci))
@@ -693,29 +693,38 @@ def test_order_bfs_is_the_reference_permutation(pkg, oracle, name, graph):
         assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
 
 
-def test_order_bfs_config_shapes_and_refusal(pkg, oracle):
-    """The C2-shaped graph symmetrised (169 343 vertices) and the C4 batch of molecule graphs (tens of thousands of
-    components) against the sequential restatement; a pattern that is not symmetric is refused."""
-    import ctypes as C
-
+def test_order_bfs_config_shapes_and_directed_patterns(pkg, oracle):
+    """The C2-shaped graph (169 343 vertices) and the C4 batch of molecule graphs (tens of thousands of components),
+    symmetrised and as generated (directed), and small directed patterns where most vertices are reached from a
+    smaller root's territory: the sequential restatement's permutation every time, and the reference's own output
+    graph on the small ones."""
     import scipy.sparse as sp
     from spmm_denseblock_b200 import graphs
     for cfg, scale in (("c2_arxiv", 1.0), ("c4_molhiv", 0.25)):
         rp, ci = graphs.make_config_graph(cfg, device="cuda", scale=scale)
+        p = pkg.order_bfs(rp, ci).cpu().numpy()
         rp, ci = rp.cpu().numpy(), ci.cpu().numpy()
+        assert np.array_equal(p, oracle.bfs_order(rp, ci)), cfg + " as generated"
         n = rp.size - 1
         A = sp.csr_matrix((np.ones(ci.size, np.int8), ci, rp), shape=(n, n))
         A = ((A + A.T) > 0).astype(np.int8).tocsr()
         A.sort_indices()
         rp, ci = A.indptr.astype(np.int32), A.indices.astype(np.int32)
         p = pkg.order_bfs(dev(rp), dev(ci)).cpu().numpy()
-        assert np.array_equal(p, oracle.bfs_order(rp, ci)), cfg
-    rp = np.array([0, 0, 1, 1], np.int32)  # 1 -> 0 only: the search from vertex 0 never reaches vertex 1
-    ci = np.array([0], np.int32)
-    out = torch.empty(3, dtype=torch.int32, device="cuda")
-    rc = pkg.lib().spmmdb_order_bfs(3, C.c_void_p(dev(rp).data_ptr()), C.c_void_p(dev(ci).data_ptr()),
-                                    C.c_void_p(out.data_ptr()), C.c_void_p(0))
-    assert rc == -2 and b"not symmetric" in pkg.lib().spmmdb_last_error()
+        assert np.array_equal(p, oracle.bfs_order(rp, ci)), cfg + " symmetrised"
+    rng = np.random.default_rng(77)
+    cases = [random_csr(rng, 3000, 3000, 1.2)[:2],                       # sparse, directed: many roots, long chains
+             random_csr(rng, 2000, 2000, 4, hubs={1999: 1500}, empty_rows={0, 1, 2})[:2],
+             (np.array([0, 0, 1, 1], np.int32), np.array([0], np.int32)),  # 1 -> 0 only
+             (np.array([0, 1, 2, 3, 3], np.int32), np.array([3, 0, 1], np.int32))]  # 0 -> 3, 1 -> 0, 2 -> 1
+    has_ref = oracle.ref_host_lib() is not None and hasattr(oracle.ref_host_lib(), "ref_bfs_graph")
+    for rp, ci in cases:
+        p = pkg.order_bfs(dev(rp), dev(ci))
+        assert np.array_equal(p.cpu().numpy(), oracle.bfs_order(rp, ci))
+        if has_ref:
+            nrp, nci, _ = pkg.permute_csr(dev(rp), dev(ci), None, p)
+            wrp, wci = oracle.ref_bfs_graph(rp, ci)
+            assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
 
 
 def test_order_rcm(pkg, oracle):
@@ -727,7 +736,8 @@ def test_order_rcm(pkg, oracle):
     big = undirected_graph(rng, 6000, 6, components=3, isolated=(1, 2), hubs={4: 700, 90: 5000, 91: 40}, self_loops=10)
     low = undirected_graph(rng, 5000, 3, components=6, isolated=(0,))
     assert np.diff(low[0]).max() <= 16
-    for rp, ci in (big, low, (np.zeros(4, np.int32), np.zeros(0, np.int32))):
+    directed = random_csr(rng, 3000, 3000, 3, hubs={7: 900})[:2]
+    for rp, ci in (big, low, directed, (np.zeros(4, np.int32), np.zeros(0, np.int32))):
         # ascending lists: the restatement's stable sort then breaks degree ties by ascending id, like the device
         p = pkg.order_rcm(dev(rp), dev(ci))
         assert np.array_equal(p.cpu().numpy(), oracle.rcm_order(rp, ci))

@@ -46,24 +46,30 @@ def main():
         return ts[len(ts) // 2]
 
     for cfg in ("c2_arxiv", "c4_molhiv", "c3_proteins", "c5_products"):
-        rp, ci = graphs.make_config_graph(cfg, device="cuda")
-        n = rp.numel() - 1
-        rp, ci = symmetrise(rp, ci, n)
-        t_bfs = timeit(lambda: pkg.order_bfs(rp, ci))
-        t_deg = timeit(lambda: pkg.order_by_degree(rp))
-        p = pkg.order_bfs(rp, ci)
-        t_apply = timeit(lambda: pkg.permute_csr(rp, ci, None, p))
-        hrp, hci = rp.cpu().numpy(), ci.cpu().numpy()
-        t = time.perf_counter()
-        want = O.bfs_order(hrp, hci)
-        t_cpu = (time.perf_counter() - t) * 1e3
-        line = json.dumps(dict(config=cfg + " (symmetrised)", n=n, nnz=int(ci.numel()), order_bfs_ms=t_bfs,
-                               order_by_degree_ms=t_deg, permute_csr_ms=t_apply, cpu_bfs_restatement_ms=t_cpu,
-                               bfs_equals_sequential=bool((p.cpu().numpy() == want).all())))
-        print(line, flush=True)
-        out.write(line + "\n")
-        del rp, ci, p
-        torch.cuda.empty_cache()
+        for variant in ("as generated (directed)", "symmetrised"):
+            rp, ci = graphs.make_config_graph(cfg, device="cuda")
+            n = rp.numel() - 1
+            if variant == "symmetrised":
+                rp, ci = symmetrise(rp, ci, n)
+            t_bfs = timeit(lambda: pkg.order_bfs(rp, ci))
+            t_rcm = timeit(lambda: pkg.order_rcm(rp, ci))
+            t_deg = timeit(lambda: pkg.order_by_degree(rp))
+            p = pkg.order_bfs(rp, ci)
+            t_apply = timeit(lambda: pkg.permute_csr(rp, ci, None, p))
+            hrp, hci = rp.cpu().numpy(), ci.cpu().numpy()
+            t = time.perf_counter()
+            want = O.bfs_order(hrp, hci)
+            t_cpu = (time.perf_counter() - t) * 1e3
+            line = json.dumps(dict(config=cfg, pattern=variant, n=n, nnz=int(ci.numel()), order_bfs_ms=t_bfs,
+                                   order_rcm_ms=t_rcm, order_by_degree_ms=t_deg, permute_csr_ms=t_apply,
+                                   cpu_bfs_restatement_ms=t_cpu,
+                                   bfs_equals_sequential=bool((p.cpu().numpy() == want).all()),
+                                   rcm_equals_restatement=bool((pkg.order_rcm(rp, ci).cpu().numpy()
+                                                                == O.rcm_order(hrp, hci)).all())))
+            print(line, flush=True)
+            out.write(line + "\n")
+            del rp, ci, p
+            torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":
