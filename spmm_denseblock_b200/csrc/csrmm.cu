@@ -600,6 +600,121 @@ __device__ __forceinline__ uint64_t policy_evict_unchanged() {
   return p;
 }
 
+// ---- what the persistent kernels (stream, lean, TMA gather) share: how a warp picks its next unit of work and how a
+// queued long-row segment is finished.
+struct WorkUnit {
+  int t;          // >= 0: ticket of a queued segment; -1: a work item of consecutive rows
+  int next_item;  // lane 0: the item claimed for the round after this one
+  int nrows;      // rows of the unit (1 for a segment)
+  int s, e;       // lane r < nrows: non-zero range of row r (segment: lane 0)
+  int lng;        // lane r: row r is long and was queued (not computed here)
+  int ldo;        // output row stride in float4 (0: the unit's single partial-sum row)
+  float4* obase;  // output row 0
+};
+enum { kWorkRun = 0, kWorkVoid = 1, kWorkNone = 2 };
+
+// A queued segment if there is one (counting semaphore counters[5], ticket index counters[4]), else the item already
+// claimed.  kWorkVoid: the ticket's row did not fit the queue (nothing to do, look again); kWorkNone: out of items.
+__device__ __forceinline__ int pick_work(const CsrArgs& a, int lane, int item, int nitems, int kpadv, int& pending, WorkUnit& w) {
+  constexpr unsigned FULL = 0xffffffffu;
+  int t = -1;
+  if (pending) {
+    if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
+      if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
+      else atomicAdd(a.counters + 5, 1);
+    }
+    t = __shfl_sync(FULL, t, 0);
+  }
+  pending = 0;
+  w.t = t;
+  w.next_item = item;
+  w.nrows = 1; w.s = 0; w.e = 0; w.lng = 0;
+  if (t >= 0) {
+    volatile unsigned long long* pe = a.seg_entry + t;
+    unsigned long long ent;
+    do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
+    __threadfence();
+    pending = 1;  // keep draining the queue
+    if ((unsigned)ent == 0xffffffffu) return kWorkVoid;
+    const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));  // written during this kernel
+    if (lane == 0) {
+      w.s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
+      w.e = min(__ldg(a.rowptr + raw.x + 1), w.s + a.seg);
+    }
+    // partial sums are stored raw; alpha / beta are applied by the final add
+    w.obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
+    w.ldo = 0;
+    return kWorkRun;
+  }
+  if (item >= nitems) return kWorkNone;
+  if (lane == 0) {
+    w.next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the caller's loop
+    // queue look, also consumed at the bottom (a little stale is fine: the second launch sweeps up)
+    pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
+  }
+  const int r0 = item * a.rpi;
+  w.nrows = min(a.rpi, a.m - r0);
+  if (lane < w.nrows) {
+    w.s = __ldg(a.rowptr + r0 + lane);
+    w.e = __ldg(a.rowptr + r0 + lane + 1);
+  }
+  w.lng = (w.e - w.s) > a.seg;
+  if (__any_sync(FULL, w.lng)) {
+    pending = a.inline_segs;
+    if (w.lng) w.lng = publish_long_row(a, r0 + lane, w.e - w.s);
+  }
+  w.ldo = (int)(a.ldc >> 2);
+  w.obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * w.ldo;
+  return kWorkRun;
+}
+
+// The partial sum of ticket t is written: publish it; the warp that finishes the row's last segment adds the partials
+// in segment order (alpha / beta applied here) and restores the row's `done` counter.  `acc` is scratch of the caller
+// (the stream kernel hands over its accumulators, which are free at this point).
+template <int VEC, int OV>
+__device__ __forceinline__ void finish_queued_segment(const CsrArgs& a, int t, int lane, int kpadv, const bool (&colok)[VEC],
+                                                      float4 (&acc)[VEC][OV]) {
+  using Ops = VecOps<float4>;
+  constexpr unsigned FULL = 0xffffffffu;
+  __threadfence();
+  __syncwarp();
+  const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
+  const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
+  const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
+  int last = 0;
+  if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
+  last = __shfl_sync(FULL, last, 0);
+  if (!last) return;
+  __threadfence();
+  if (lane == 0) a.done[seg_slot] = 0;
+  const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
+  for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i)
+      if (colok[i]) {
+#pragma unroll
+        for (int h = 0; h < OV; ++h) {
+          const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
+          if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
+        }
+      }
+  }
+  float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
+#pragma unroll
+  for (int i = 0; i < VEC; ++i)
+    if (colok[i]) {
+#pragma unroll
+      for (int h = 0; h < OV; ++h) {
+        float4* o = Cv + OV * (lane + 32 * i) + h;
+        float4 out;
+        if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
+        else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
+        else out = acc[i][h];
+        __stcs(o, out);
+      }
+    }
+}
+
 template <int VEC, int U, int MINB, bool BF16, bool HINT>
 __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a_in) {
   CsrArgs a = a_in;
@@ -636,55 +751,12 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
   int pending = a.inline_segs;  // look at the queue before the first item: the second launch has only the queue left
   for (;;) {
     // ---- pick work: a queued segment if there is one, else the item already claimed
-    int t = -1;
-    if (pending) {
-      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
-        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
-        else atomicAdd(a.counters + 5, 1);
-      }
-      t = __shfl_sync(FULL, t, 0);
-    }
-    pending = 0;
-    int next_item = item;
-    int nrows = 1, s = 0, e = 0, lng = 0;
-    float4* __restrict__ obase;  // output row 0 of this work unit
-    int ldo;
-    if (t >= 0) {
-      volatile unsigned long long* pe = a.seg_entry + t;
-      unsigned long long ent;
-      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
-      __threadfence();
-      pending = 1;  // keep draining the queue
-      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket (its row did not fit the queue)
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));  // written during this kernel
-      if (lane == 0) {
-        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
-        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
-      }
-      // partial sums are stored raw; alpha / beta are applied by the final add
-      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
-      ldo = 0;
-    } else {
-      if (item >= nitems) break;
-      if (lane == 0) {
-        next_item = atomicAdd(a.counters + 3, 1);  // consumed at the bottom of the loop
-        // queue look, also consumed at the bottom (a little stale is fine: the second launch sweeps up)
-        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
-      }
-      const int r0 = item * a.rpi;
-      nrows = min(a.rpi, a.m - r0);
-      if (lane < nrows) {
-        s = __ldg(a.rowptr + r0 + lane);
-        e = __ldg(a.rowptr + r0 + lane + 1);
-      }
-      lng = (e - s) > a.seg;
-      if (__any_sync(FULL, lng)) {
-        pending = a.inline_segs;
-        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
-      }
-      ldo = (int)(a.ldc >> 2);
-      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
-    }
+    WorkUnit w;
+    const int what = pick_work(a, lane, item, nitems, kpadv, pending, w);
+    if (what == kWorkNone) break;
+    if (what == kWorkVoid) continue;
+    const int t = w.t, next_item = w.next_item, nrows = w.nrows, s = w.s, e = w.e, lng = w.lng, ldo = w.ldo;
+    float4* __restrict__ obase = w.obase;  // output row 0 of this work unit
     const int S = __shfl_sync(FULL, s, 0);
     const int E = __shfl_sync(FULL, e, nrows - 1);
 
@@ -814,45 +886,7 @@ __global__ void __launch_bounds__(256, MINB) csrmm_stream_kernel(const CsrArgs a
     while (cr < nrows) flush_advance();  // last row and trailing empty rows
 
     if (t >= 0) {
-      // publish the partial; the warp that finishes the row's last segment adds them in segment order
-      __threadfence();
-      __syncwarp();
-      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
-      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
-      int last = 0;
-      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
-      last = __shfl_sync(FULL, last, 0);
-      if (last) {
-        __threadfence();
-        if (lane == 0) a.done[seg_slot] = 0;
-        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
-        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
-#pragma unroll
-          for (int i = 0; i < VEC; ++i)
-            if (colok[i]) {
-#pragma unroll
-              for (int h = 0; h < OV; ++h) {
-                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
-                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
-              }
-            }
-        }
-        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i)
-          if (colok[i]) {
-#pragma unroll
-            for (int h = 0; h < OV; ++h) {
-              float4* o = Cv + OV * (lane + 32 * i) + h;
-              float4 out;
-              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
-              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
-              else out = acc[i][h];
-              __stcs(o, out);
-            }
-          }
-      }
+      finish_queued_segment<VEC, OV>(a, t, lane, kpadv, colok, acc);
     } else {
       item = __shfl_sync(FULL, next_item, 0);
     }
@@ -904,54 +938,13 @@ __global__ void __launch_bounds__(256, MINB) csrmm_lean_kernel(const CsrArgs a_i
   item = __shfl_sync(FULL, item, 0);
   int pending = a.inline_segs;
   for (;;) {
-    // ---- pick work: a queued segment if there is one, else the item already claimed (as csrmm_stream_kernel)
-    int t = -1;
-    if (pending) {
-      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
-        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
-        else atomicAdd(a.counters + 5, 1);
-      }
-      t = __shfl_sync(FULL, t, 0);
-    }
-    pending = 0;
-    int next_item = item;
-    int nrows = 1, s = 0, e = 0, lng = 0;
-    float4* __restrict__ obase;
-    int ldo;
-    if (t >= 0) {
-      volatile unsigned long long* pe = a.seg_entry + t;
-      unsigned long long ent;
-      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
-      __threadfence();
-      pending = 1;
-      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));
-      if (lane == 0) {
-        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
-        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
-      }
-      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
-      ldo = 0;
-    } else {
-      if (item >= nitems) break;
-      if (lane == 0) {
-        next_item = atomicAdd(a.counters + 3, 1);
-        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
-      }
-      const int r0 = item * a.rpi;
-      nrows = min(a.rpi, a.m - r0);
-      if (lane < nrows) {
-        s = __ldg(a.rowptr + r0 + lane);
-        e = __ldg(a.rowptr + r0 + lane + 1);
-      }
-      lng = (e - s) > a.seg;
-      if (__any_sync(FULL, lng)) {
-        pending = a.inline_segs;
-        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
-      }
-      ldo = (int)(a.ldc >> 2);
-      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
-    }
+    // ---- pick work: a queued segment if there is one, else the item already claimed
+    WorkUnit w;
+    const int what = pick_work(a, lane, item, nitems, kpadv, pending, w);
+    if (what == kWorkNone) break;
+    if (what == kWorkVoid) continue;
+    const int t = w.t, next_item = w.next_item, nrows = w.nrows, s = w.s, e = w.e, lng = w.lng, ldo = w.ldo;
+    float4* __restrict__ obase = w.obase;  // output row 0 of this work unit
     const unsigned longmask = __ballot_sync(FULL, lng != 0);
 
     // ---- runs of consecutive rows that are computed here (a queued long row ends a run)
@@ -1092,45 +1085,8 @@ __global__ void __launch_bounds__(256, MINB) csrmm_lean_kernel(const CsrArgs a_i
     }
 
     if (t >= 0) {
-      __threadfence();
-      __syncwarp();
-      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
-      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
-      int last = 0;
-      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
-      last = __shfl_sync(FULL, last, 0);
-      if (last) {
-        __threadfence();
-        if (lane == 0) a.done[seg_slot] = 0;
-        float4 acc[VEC][OV];
-        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
-        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
-#pragma unroll
-          for (int i = 0; i < VEC; ++i)
-            if (colok[i]) {
-#pragma unroll
-              for (int h = 0; h < OV; ++h) {
-                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
-                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
-              }
-            }
-        }
-        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i)
-          if (colok[i]) {
-#pragma unroll
-            for (int h = 0; h < OV; ++h) {
-              float4* o = Cv + OV * (lane + 32 * i) + h;
-              float4 out;
-              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
-              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
-              else out = acc[i][h];
-              __stcs(o, out);
-            }
-          }
-      }
+      float4 sums[VEC][OV];
+      finish_queued_segment<VEC, OV>(a, t, lane, kpadv, colok, sums);
     } else {
       item = __shfl_sync(FULL, next_item, 0);
     }
@@ -1220,54 +1176,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1) csrmm_tma_kernel(const CsrArgs 
   item = __shfl_sync(FULL, item, 0);
   int pending = a.inline_segs;
   for (;;) {
-    // ---- pick work: a queued segment if there is one, else the item already claimed (as csrmm_stream_kernel)
-    int t = -1;
-    if (pending) {
-      if (lane == 0 && *(volatile int*)(a.counters + 5) > 0) {
-        if (atomicSub(a.counters + 5, 1) > 0) t = atomicAdd(a.counters + 4, 1);
-        else atomicAdd(a.counters + 5, 1);
-      }
-      t = __shfl_sync(FULL, t, 0);
-    }
-    pending = 0;
-    int next_item = item;
-    int nrows = 1, s = 0, e = 0, lng = 0;
-    float4* __restrict__ obase;
-    int ldo;
-    if (t >= 0) {
-      volatile unsigned long long* pe = a.seg_entry + t;
-      unsigned long long ent;
-      do { ent = *pe; } while ((unsigned)(ent >> 32) != (unsigned)a.epoch);
-      __threadfence();
-      pending = 1;
-      if ((unsigned)ent == 0xffffffffu) continue;  // void ticket
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + (unsigned)ent));
-      if (lane == 0) {
-        s = __ldg(a.rowptr + raw.x) + (t - raw.y) * a.seg;
-        e = min(__ldg(a.rowptr + raw.x + 1), s + a.seg);
-      }
-      obase = reinterpret_cast<float4*>(a.partial) + (int64_t)t * kpadv;
-      ldo = 0;
-    } else {
-      if (item >= nitems) break;
-      if (lane == 0) {
-        next_item = atomicAdd(a.counters + 3, 1);
-        pending = a.inline_segs && *(volatile int*)(a.counters + 5) > 0;
-      }
-      const int r0 = item * a.rpi;
-      nrows = min(a.rpi, a.m - r0);
-      if (lane < nrows) {
-        s = __ldg(a.rowptr + r0 + lane);
-        e = __ldg(a.rowptr + r0 + lane + 1);
-      }
-      lng = (e - s) > a.seg;
-      if (__any_sync(FULL, lng)) {
-        pending = a.inline_segs;
-        if (lng) lng = publish_long_row(a, r0 + lane, e - s);
-      }
-      ldo = (int)(a.ldc >> 2);
-      obase = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * ldo;
-    }
+    // ---- pick work: a queued segment if there is one, else the item already claimed
+    WorkUnit w;
+    const int what = pick_work(a, lane, item, nitems, kpadv, pending, w);
+    if (what == kWorkNone) break;
+    if (what == kWorkVoid) continue;
+    const int t = w.t, next_item = w.next_item, nrows = w.nrows, s = w.s, e = w.e, lng = w.lng, ldo = w.ldo;
+    float4* __restrict__ obase = w.obase;  // output row 0 of this work unit
     const unsigned longmask = __ballot_sync(FULL, lng != 0);
 
     // ---- runs of consecutive rows that are computed here (a queued long row ends a run)
@@ -1410,45 +1325,8 @@ __global__ void __launch_bounds__(WARPS * 32, 1) csrmm_tma_kernel(const CsrArgs 
     }
 
     if (t >= 0) {
-      __threadfence();
-      __syncwarp();
-      const int seg_slot = (int)(unsigned)*(volatile unsigned long long*)(a.seg_entry + t);
-      const int4 raw = __ldcg(reinterpret_cast<const int4*>(a.long_rows + seg_slot));
-      const int r0 = raw.x, seg_base = raw.y, seg_nseg = raw.z;
-      int last = 0;
-      if (lane == 0) last = (atomicAdd(a.done + seg_slot, 1) == seg_nseg - 1);
-      last = __shfl_sync(FULL, last, 0);
-      if (last) {
-        __threadfence();
-        if (lane == 0) a.done[seg_slot] = 0;
-        float4 acc[VEC][OV];
-        const float4* __restrict__ p = reinterpret_cast<const float4*>(a.partial) + (int64_t)seg_base * kpadv;
-        for (int q = 0; q < seg_nseg; ++q, p += kpadv) {
-#pragma unroll
-          for (int i = 0; i < VEC; ++i)
-            if (colok[i]) {
-#pragma unroll
-              for (int h = 0; h < OV; ++h) {
-                const float4 x = __ldcg(p + OV * (lane + 32 * i) + h);
-                if (q == 0) acc[i][h] = x; else Ops::add(acc[i][h], x);
-              }
-            }
-        }
-        float4* __restrict__ Cv = reinterpret_cast<float4*>(a.C) + (int64_t)r0 * (a.ldc >> 2);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i)
-          if (colok[i]) {
-#pragma unroll
-            for (int h = 0; h < OV; ++h) {
-              float4* o = Cv + OV * (lane + 32 * i) + h;
-              float4 out;
-              if (a.beta != 0.f) out = Ops::axpby(a.alpha, acc[i][h], a.beta, *o);
-              else if (a.alpha != 1.f) out = Ops::scale(a.alpha, acc[i][h]);
-              else out = acc[i][h];
-              __stcs(o, out);
-            }
-          }
-      }
+      float4 sums[VEC][OV];
+      finish_queued_segment<VEC, OV>(a, t, lane, kpadv, colok, sums);
     } else {
       item = __shfl_sync(FULL, next_item, 0);
     }
