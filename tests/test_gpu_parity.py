@@ -727,6 +727,26 @@ def test_order_bfs_config_shapes_and_directed_patterns(pkg, oracle):
             assert np.array_equal(nrp.cpu().numpy(), wrp) and np.array_equal(nci.cpu().numpy(), wci)
 
 
+def test_orderings_golden_reference(pkg, golden_dir):
+    """The device orderings against the committed outputs of the reference's own functions
+    (tests/golden/ref_orderings.npz): the graph permuted with spmmdb_order_bfs equals BFSTraversal's output on
+    undirected, unsorted-list and directed inputs; spmmdb_order_rcm equals reverseCuthillMcKee's where the
+    reference's sort is stable; spmmdb_order_by_degree gives maxDegreeSort's row lengths."""
+    import os
+    d = np.load(os.path.join(golden_dir, "ref_orderings.npz"))
+    for name in ("und", "unsorted", "directed", "lowdeg"):
+        rp, ci = dev(d[name + "_rowptr"]), dev(d[name + "_colind"])
+        nrp, nci, _ = pkg.permute_csr(rp, ci, None, pkg.order_bfs(rp, ci))
+        assert np.array_equal(nrp.cpu().numpy(), d[name + "_bfs_rowptr"]), name
+        assert np.array_equal(nci.cpu().numpy(), d[name + "_bfs_colind"]), name
+        nrp, _, _ = pkg.permute_csr(rp, ci, None, pkg.order_by_degree(rp))
+        assert np.array_equal(nrp.cpu().numpy(), d[name + "_deg_rowptr"]), name
+        if name == "lowdeg":
+            nrp, nci, _ = pkg.permute_csr(rp, ci, None, pkg.order_rcm(rp, ci))
+            assert np.array_equal(nrp.cpu().numpy(), d[name + "_rcm_rowptr"])
+            assert np.array_equal(nci.cpu().numpy(), d[name + "_rcm_colind"])
+
+
 def test_order_rcm(pkg, oracle):
     """spmmdb_order_rcm == reverseCuthillMcKee (reorder_strategy.cc:57-66) with equal-degree neighbours in ascending
     id: the restatement's permutation on graphs with hubs and unsorted lists; the reference's own output graph where

@@ -245,3 +245,21 @@ def test_rcm_order_restatement_matches_the_reference_where_std_sort_is_stable(or
         p = oracle.rcm_order(rp, ci)
         got, want = oracle.permutate_csr(rp, ci, p), oracle.ref_rcmk_graph(rp, ci)
         assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+def test_golden_ref_orderings(oracle, golden_dir):
+    """The restated orderings against the committed outputs of the reference's own BFSTraversal /
+    reverseCuthillMcKee / maxDegreeSort (tests/golden/ref_orderings.npz, made by make_golden_orderings.py): BFS graphs
+    bit for bit on every case (undirected, unsorted lists, directed); RCM bit for bit where the reference's sort is
+    stable (maximum degree <= 16); the degree order's row lengths always."""
+    d = np.load(os.path.join(golden_dir, "ref_orderings.npz"))
+    for name in ("und", "unsorted", "directed", "lowdeg"):
+        rp, ci = d[name + "_rowptr"], d[name + "_colind"]
+        got = oracle.permutate_csr(rp, ci, oracle.bfs_order(rp, ci))
+        assert np.array_equal(got[0], d[name + "_bfs_rowptr"]) and np.array_equal(got[1], d[name + "_bfs_colind"]), name
+        got = oracle.permutate_csr(rp, ci, oracle.degree_order(rp))
+        assert np.array_equal(got[0], d[name + "_deg_rowptr"]), name
+        got = oracle.permutate_csr(rp, ci, oracle.rcm_order(rp, ci))
+        assert np.array_equal(np.sort(np.diff(got[0])), np.sort(np.diff(d[name + "_rcm_rowptr"]))), name
+        if name == "lowdeg":
+            assert np.array_equal(got[0], d[name + "_rcm_rowptr"]) and np.array_equal(got[1], d[name + "_rcm_colind"])
